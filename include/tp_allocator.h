@@ -1,0 +1,161 @@
+/*
+ * tp_allocator.h -- C ABI of the B200 topology-aware preferred-allocation policy.
+ *
+ * Drop-in boundary for ONE path of the reference device plugin: the best-effort
+ * device selection behind the kubelet GetPreferredAllocation RPC, i.e. the Go
+ * interface
+ *
+ *     type Policy interface {                       // internal/pkg/allocator/allocator.go:27-30
+ *         Init(devs []*Device, topoDir string) error
+ *         Allocate(available, required []string, size int) ([]string, error)
+ *     }
+ *
+ * as implemented by BestEffortPolicy (internal/pkg/allocator/besteffort_policy.go:45-151,
+ * device.go:254-442).  A Go policy keeps the string<->index maps and the sysfs
+ * parsers (device.go:107-252) and calls these entry points through cgo; see
+ * INTEGRATION.md for the stub.  Plain pointers and sizes only; every entry
+ * point returns 0 / a count on success or a negative tp_status; nothing throws
+ * or aborts across the boundary.  There is no CPU fallback: every request the
+ * reference would search runs on the GPU, and all entry points fail with
+ * TP_ERR_CUDA when no device is usable.
+ *
+ * Devices are named by INDEX into the arrays given to tp_create (0..n-1).
+ */
+#ifndef TP_ALLOCATOR_H
+#define TP_ALLOCATOR_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TP_MAX_DEVICES 128 /* devices per policy (KFD nodes with a render minor) */
+#define TP_MAX_SUBSET 16   /* largest size - len(required) the exhaustive kernels take */
+
+typedef enum tp_status {
+    TP_OK = 0,
+    /* 1:1 with the reference's error strings, besteffort_policy.go:36-43 */
+    TP_ERR_INVALID_SIZE = -1,          /* invalidSize,         check at :90-92   */
+    TP_ERR_INVALID_AVAILABLE = -2,     /* invalidAvailable,    check at :94-96   */
+    TP_ERR_INVALID_REQUIRED = -3,      /* invalidRequired,     check at :98-100  */
+    TP_ERR_INVALID_REQ_AVAILABLE = -4, /* invalidReqAvailable, check at :102-104 */
+    TP_ERR_INVALID_INIT = -5,          /* invalidInit,         checks at :106-108, :118-120 */
+    TP_ERR_NO_CANDIDATE = -6,          /* noCandidateFound,    check at :122-124 */
+    TP_ERR_INIT_FAILED = -7,           /* "Besteffort Policy init failed to initialize p2pWeights", :72-74 */
+    /* not in the reference */
+    TP_ERR_BAD_INDEX = -20,   /* unknown / duplicate device index (the reference nil-derefs, :61-68) */
+    TP_ERR_BAD_ARGUMENT = -21,
+    TP_ERR_TOO_LARGE = -22,   /* search space beyond what any kernel here enumerates */
+    TP_ERR_CUDA = -30,
+    TP_ERR_NCCL = -31
+} tp_status;
+
+/*
+ * What BestEffortPolicy.Init leaves behind (besteffort_policy.go:70-86), index based:
+ *   node_id      Device.NodeId (device.go:58); distinct.
+ *   group        dense index of Device.DevId: same physical GPU => same value
+ *                (groupPartitionsByDevId, device.go:287-304).
+ *   parent_rank  per group: rank of its ParentId under Go's string `<`, which
+ *                orders groups with equally many free partitions (device.go:342-349).
+ *   weight       n*n, row major, symmetric: p2pWeights[min][max] (device.go:135-157, :214),
+ *                0 where the map has no entry (Go zero value, device.go:266).
+ * All arrays are copied.
+ */
+typedef struct tp_topology {
+    int32_t n_devices;
+    int32_t n_groups;
+    const int32_t *node_id;
+    const int32_t *group;
+    const int32_t *parent_rank;
+    const uint8_t *weight;
+} tp_topology;
+
+typedef struct tp_options {
+    int32_t cuda_device;        /* ordinal; -1 = the current device */
+    int32_t kernel;             /* 0 = auto; else force a kernel variant (tests / profiling) */
+    uint64_t exhaustive_limit;  /* 0 = default; above this many subsets only Family members are enumerated */
+    int32_t max_inflight;       /* 0 = default (8): concurrent tp_allocate calls before callers queue */
+    int32_t reserved;
+} tp_options;
+
+/* Packed winner: (score, groups touched, group sequence) -- smaller is better; the
+ * order is the order in which the reference's BFS emits candidates
+ * (device.go:375-440) under the strict `<` of besteffort_policy.go:133-140. */
+typedef struct tp_key {
+    uint64_t hi; /* score:16 | groups:8 | first 40 bits of the group sequence */
+    uint64_t lo; /* rest of the group sequence; 0 whenever (size-len(required))*ceil(log2 groups) <= 40 */
+} tp_key;
+
+typedef struct tp_result {
+    int32_t score;           /* DeviceSet.TotalWeight of the winner (device.go:67-73) */
+    int32_t groups_touched;
+    int32_t searched;        /* 0: answered by a short-circuit (besteffort_policy.go:110-116), no GPU work */
+    int32_t kernel;          /* kernel variant that ran */
+    uint64_t subsets_scored; /* counted on the device */
+    uint64_t subsets_total;  /* C(free, size-len(required)) */
+    float kernel_ms;         /* CUDA-event time of the search kernel(s) on the call's stream */
+    int32_t gpu_launches;
+    tp_key key;
+} tp_result;
+
+typedef struct tp_request {
+    const int32_t *available; /* AvailableDeviceIDs as indices */
+    int32_t n_available;
+    const int32_t *required;  /* MustIncludeDeviceIDs as indices */
+    int32_t n_required;
+    int32_t size;             /* AllocationSize */
+} tp_request;
+
+typedef struct tp_policy tp_policy;
+
+/* BestEffortPolicy.Init (besteffort_policy.go:70-86) minus the sysfs parse, which stays
+ * with the caller: copies the topology to the GPU and sets up streams/buffers. */
+int tp_create(const tp_topology *topo, const tp_options *opts, tp_policy **out);
+void tp_destroy(tp_policy *p);
+
+/* BestEffortPolicy.Allocate (besteffort_policy.go:88-151).  Writes `size` device
+ * indices to out in the reference's output order (:141-148) and returns size, or a
+ * negative tp_status.  Reentrant and blocking; info may be NULL. */
+int tp_allocate(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+                int32_t n_required, int32_t size, int32_t *out, tp_result *info);
+
+/* The ContainerRequests loop of AMDGPUKFDImpl.GetPreferredAllocation
+ * (internal/pkg/amdgpu/amdgpu.go:307-317) as one call.  out is n_requests rows of
+ * out_stride int32; status[i] receives what tp_allocate would have returned. */
+int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *requests, int32_t *out,
+                      int32_t out_stride, int32_t *status, tp_result *infos);
+
+/* Multi-GPU: score only shard `shard_index` of `shard_count` equal slices of the
+ * subset space and return the shard's packed winner; the caller min-reduces keys
+ * across shards (one ncclMin all-reduce on key.hi when key.lo is always 0) and
+ * decodes the winner with tp_decode.  Requests answered by a short-circuit return
+ * 1 and leave key untouched (call tp_allocate for them). */
+int tp_search_shard(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+                    int32_t n_required, int32_t size, int32_t shard_index, int32_t shard_count,
+                    tp_key *key, tp_result *info);
+int tp_decode(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+              int32_t n_required, int32_t size, const tp_key *key, int32_t *out);
+
+/* Measurement hook: the request is prepared and uploaded once, then the search
+ * kernel is launched `iters` times back to back on the policy's stream between two
+ * CUDA events; *ms receives the total device time.  No host<->device copy in the
+ * timed region.  Same result contract as tp_search_shard. */
+int tp_search_resident(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+                       int32_t n_required, int32_t size, int32_t shard_index, int32_t shard_count,
+                       int32_t iters, float *ms, tp_key *key, tp_result *info);
+
+/* calculatePairWeight (device.go:135-157) for all pairs on the GPU: weight[i*n+j] from
+ * per-device group / NUMA node and an n*n matrix of KFD link types (io_links/p2p_links
+ * `type`; 11 = XGMI, 2 = PCIe; -1 = no link entry => weight 0, the Go map's zero value). */
+int tp_build_weights(int32_t n, const int32_t *group, const int32_t *numa_node, const int32_t *link_type,
+                     uint8_t *weight_out, int32_t cuda_device);
+
+const char *tp_strerror(int status);
+/* Last CUDA error text seen by this policy (diagnostics). */
+const char *tp_last_cuda_error(const tp_policy *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,286 @@
+"""B200 topology-aware preferred-allocation policy: ctypes view of libtpalloc.so.
+
+The product is the shared library (csrc/: C ABI + sm_100a kernels, host/: C++ mirror of the
+reference's allocator.Policy).  This module only marshals arguments so that tests and
+bench.py read like the reference's Go tests (besteffort_policy_test.go):
+
+    pol = BestEffortPolicy()
+    pol.Init(devices, topo_dir)            # allocator.Policy.Init      (allocator.go:28)
+    ids = pol.Allocate(avail, req, size)   # allocator.Policy.Allocate  (allocator.go:29)
+
+There is no Python or CPU implementation of the search behind it: loading fails loudly when
+the library is missing, and every searched request runs on the GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libtpalloc.so")
+ID_LEN = 64
+
+TP_MAX_DEVICES = 128
+TP_MAX_SUBSET = 16
+STATUS = {
+    "TP_OK": 0, "TP_ERR_INVALID_SIZE": -1, "TP_ERR_INVALID_AVAILABLE": -2, "TP_ERR_INVALID_REQUIRED": -3,
+    "TP_ERR_INVALID_REQ_AVAILABLE": -4, "TP_ERR_INVALID_INIT": -5, "TP_ERR_NO_CANDIDATE": -6,
+    "TP_ERR_INIT_FAILED": -7, "TP_ERR_BAD_INDEX": -20, "TP_ERR_BAD_ARGUMENT": -21, "TP_ERR_TOO_LARGE": -22,
+    "TP_ERR_CUDA": -30, "TP_ERR_NCCL": -31,
+}
+KERNEL_AUTO, KERNEL_LEX, KERNEL_FAMILY = 0, 1, 3
+
+
+class TpKey(C.Structure):
+    _fields_ = [("hi", C.c_uint64), ("lo", C.c_uint64)]
+
+    def tuple(self):
+        return (self.hi, self.lo)
+
+
+class TpResult(C.Structure):
+    _fields_ = [("score", C.c_int32), ("groups_touched", C.c_int32), ("searched", C.c_int32),
+                ("kernel", C.c_int32), ("subsets_scored", C.c_uint64), ("subsets_total", C.c_uint64),
+                ("kernel_ms", C.c_float), ("gpu_launches", C.c_int32), ("key", TpKey)]
+
+    def dict(self):
+        d = {f: getattr(self, f) for f, _ in self._fields_ if f != "key"}
+        d["key"] = (self.key.hi, self.key.lo)
+        return d
+
+
+class TpOptions(C.Structure):
+    _fields_ = [("cuda_device", C.c_int32), ("kernel", C.c_int32), ("exhaustive_limit", C.c_uint64),
+                ("max_inflight", C.c_int32), ("reserved", C.c_int32)]
+
+
+class TpTopology(C.Structure):
+    _fields_ = [("n_devices", C.c_int32), ("n_groups", C.c_int32), ("node_id", C.POINTER(C.c_int32)),
+                ("group", C.POINTER(C.c_int32)), ("parent_rank", C.POINTER(C.c_int32)),
+                ("weight", C.POINTER(C.c_uint8))]
+
+
+class TpRequest(C.Structure):
+    _fields_ = [("available", C.POINTER(C.c_int32)), ("n_available", C.c_int32),
+                ("required", C.POINTER(C.c_int32)), ("n_required", C.c_int32), ("size", C.c_int32)]
+
+
+class _HDevice(C.Structure):
+    _fields_ = [("id", C.c_char * ID_LEN), ("node_id", C.c_int32), ("numa_node", C.c_int32),
+                ("dev_id", C.c_char * ID_LEN)]
+
+
+@dataclass
+class Device:
+    """allocator.Device (device.go:56-65)."""
+    Id: str
+    NodeId: int
+    NumaNode: int
+    DevId: str
+
+
+class AllocatorError(Exception):
+    """A Go `error` from the policy; str() is the reference's message."""
+
+    def __init__(self, status: int, msg: str):
+        super().__init__(msg)
+        self.status = status
+
+
+_lib = None
+I32P = C.POINTER(C.c_int32)
+
+
+def lib() -> C.CDLL:
+    """Load libtpalloc.so; raises if it has not been built (no fallback of any kind)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python rocm-k8s-device-plugin_b200/build.py` "
+                           "(nvcc, sm_100a). There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    L.tp_strerror.restype = C.c_char_p
+    L.tp_strerror.argtypes = [C.c_int]
+    L.tp_last_cuda_error.restype = C.c_char_p
+    L.tp_last_cuda_error.argtypes = [C.c_void_p]
+    L.tp_create.argtypes = [C.POINTER(TpTopology), C.POINTER(TpOptions), C.POINTER(C.c_void_p)]
+    L.tp_destroy.argtypes = [C.c_void_p]
+    L.tp_destroy.restype = None
+    req_args = [C.c_void_p, I32P, C.c_int32, I32P, C.c_int32, C.c_int32]
+    L.tp_allocate.argtypes = req_args + [I32P, C.POINTER(TpResult)]
+    L.tp_allocate_batch.argtypes = [C.c_void_p, C.c_int32, C.POINTER(TpRequest), I32P, C.c_int32, I32P,
+                                    C.POINTER(TpResult)]
+    L.tp_search_shard.argtypes = req_args + [C.c_int32, C.c_int32, C.POINTER(TpKey), C.POINTER(TpResult)]
+    L.tp_decode.argtypes = req_args + [C.POINTER(TpKey), I32P]
+    L.tp_search_resident.argtypes = req_args + [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float),
+                                                C.POINTER(TpKey), C.POINTER(TpResult)]
+    L.tp_build_weights.argtypes = [C.c_int32, I32P, I32P, I32P, C.POINTER(C.c_uint8), C.c_int32]
+    L.tph_new.restype = C.c_void_p
+    L.tph_new.argtypes = [C.POINTER(TpOptions)]
+    L.tph_free.argtypes = [C.c_void_p]
+    L.tph_free.restype = None
+    L.tph_init.argtypes = [C.c_void_p, C.POINTER(_HDevice), C.c_int, C.c_char_p]
+    L.tph_init_pairs.argtypes = [C.c_void_p, C.POINTER(_HDevice), C.c_int, I32P, I32P, I32P, C.c_int]
+    strs = C.POINTER(C.c_char_p)
+    L.tph_allocate.argtypes = [C.c_void_p, strs, C.c_int, strs, C.c_int, C.c_int, C.c_char_p, C.POINTER(TpResult)]
+    L.tph_search_shard.argtypes = [C.c_void_p, strs, C.c_int, strs, C.c_int, C.c_int, C.c_int, C.c_int,
+                                   C.POINTER(TpKey)]
+    L.tph_decode.argtypes = [C.c_void_p, strs, C.c_int, strs, C.c_int, C.c_int, C.POINTER(TpKey), C.c_char_p]
+    for f in ("tph_weight_rows", "tph_group_count", "tph_pair_count"):
+        getattr(L, f).argtypes = [C.c_void_p]
+    L.tph_pairs.argtypes = [C.c_void_p, I32P, I32P, I32P, C.c_int]
+    L.tph_index_of.argtypes = [C.c_void_p, C.c_char_p]
+    L.tph_handle.restype = C.c_void_p
+    L.tph_handle.argtypes = [C.c_void_p]
+    L.tph_last_error.restype = C.c_char_p
+    L.tph_last_error.argtypes = [C.c_void_p]
+    _lib = L
+    return L
+
+
+def strerror(status: int) -> str:
+    return lib().tp_strerror(status).decode()
+
+
+def _i32(xs):
+    return (C.c_int32 * max(len(xs), 1))(*xs)
+
+
+def _strs(xs):
+    arr = (C.c_char_p * max(len(xs), 1))()
+    for i, s in enumerate(xs):
+        arr[i] = s.encode()
+    return arr
+
+
+def _hdevs(devs):
+    arr = (_HDevice * max(len(devs), 1))()
+    for i, d in enumerate(devs):
+        arr[i].id = d.Id.encode()
+        arr[i].node_id = d.NodeId
+        arr[i].numa_node = d.NumaNode
+        arr[i].dev_id = d.DevId.encode()
+    return arr
+
+
+def _ids(buf, n):
+    return [buf.raw[i * ID_LEN:(i + 1) * ID_LEN].split(b"\0", 1)[0].decode() for i in range(n)]
+
+
+class BestEffortPolicy:
+    """allocator.BestEffortPolicy (besteffort_policy.go:45-151) backed by the GPU search."""
+
+    def __init__(self, cuda_device: int = -1, kernel: int = KERNEL_AUTO, exhaustive_limit: int = 0,
+                 max_inflight: int = 0):
+        self._opts = TpOptions(cuda_device, kernel, exhaustive_limit, max_inflight, 0)
+        self._p = lib().tph_new(C.byref(self._opts))
+        self.last = None
+
+    def close(self):
+        if getattr(self, "_p", None):
+            lib().tph_free(self._p)
+            self._p = None
+
+    __del__ = close
+
+    def _raise(self, rc):
+        raise AllocatorError(rc, lib().tph_last_error(self._p).decode())
+
+    def Init(self, devs, topo_dir: str = ""):
+        self.devices = list(devs)
+        rc = lib().tph_init(self._p, _hdevs(devs), len(devs), topo_dir.encode())
+        if rc < 0:
+            self._raise(rc)
+
+    def InitWithWeights(self, devs, pairs):
+        """Init from p2pWeights given as (from_node, to_node, weight) triples."""
+        self.devices = list(devs)
+        rc = lib().tph_init_pairs(self._p, _hdevs(devs), len(devs), _i32([p[0] for p in pairs]),
+                                  _i32([p[1] for p in pairs]), _i32([p[2] for p in pairs]), len(pairs))
+        if rc < 0:
+            self._raise(rc)
+
+    def Allocate(self, available, required, size):
+        required = required or []
+        out = C.create_string_buffer(ID_LEN * max(size, 1))
+        res = TpResult()
+        rc = lib().tph_allocate(self._p, _strs(available), len(available), _strs(required), len(required), size,
+                                out, C.byref(res))
+        self.last = res.dict()
+        if rc < 0:
+            self._raise(rc)
+        return _ids(out, rc)
+
+    def SearchShard(self, available, required, size, shard_index, shard_count):
+        """(key | None if short-circuited): this shard's packed winner."""
+        required = required or []
+        key = TpKey()
+        rc = lib().tph_search_shard(self._p, _strs(available), len(available), _strs(required), len(required),
+                                    size, shard_index, shard_count, C.byref(key))
+        if rc < 0:
+            self._raise(rc)
+        return None if rc == 1 else (key.hi, key.lo)
+
+    def Decode(self, available, required, size, key):
+        required = required or []
+        k = TpKey(key[0], key[1])
+        out = C.create_string_buffer(ID_LEN * max(size, 1))
+        rc = lib().tph_decode(self._p, _strs(available), len(available), _strs(required), len(required), size,
+                              C.byref(k), out)
+        if rc < 0:
+            self._raise(rc)
+        return _ids(out, rc)
+
+    # introspection
+    def weight_rows(self):
+        return lib().tph_weight_rows(self._p)
+
+    def group_count(self):
+        return lib().tph_group_count(self._p)
+
+    def pairs(self):
+        n = lib().tph_pair_count(self._p)
+        f, t, w = _i32([0] * n), _i32([0] * n), _i32([0] * n)
+        lib().tph_pairs(self._p, f, t, w, n)
+        return sorted(zip(f[:n], t[:n], w[:n]))
+
+    def index_of(self, ident):
+        return lib().tph_index_of(self._p, ident.encode())
+
+    def indices(self, ids):
+        return [self.index_of(i) for i in ids]
+
+    @property
+    def handle(self):
+        """The raw tp_policy* for index-level calls (tp_allocate, tp_search_resident, ...)."""
+        return lib().tph_handle(self._p)
+
+
+def search_resident(pol: BestEffortPolicy, available, required, size, iters=1, shard_index=0, shard_count=1):
+    """tp_search_resident: request uploaded once, kernel launched `iters` times between CUDA events.
+
+    Returns (total_ms, key, result dict)."""
+    av, rq = pol.indices(available), pol.indices(required or [])
+    ms = C.c_float()
+    key = TpKey()
+    res = TpResult()
+    rc = lib().tp_search_resident(pol.handle, _i32(av), len(av), _i32(rq), len(rq), size, shard_index, shard_count,
+                                  iters, C.byref(ms), C.byref(key), C.byref(res))
+    if rc < 0:
+        msg = strerror(rc)
+        if rc == STATUS["TP_ERR_CUDA"]:
+            msg += ": " + lib().tp_last_cuda_error(pol.handle).decode()
+        raise AllocatorError(rc, msg)
+    return ms.value, (key.hi, key.lo), res.dict()
+
+
+def allocate_indices(pol: BestEffortPolicy, av, rq, size):
+    """tp_allocate on raw indices; returns (indices, result dict)."""
+    out = _i32([0] * max(size, 1))
+    res = TpResult()
+    rc = lib().tp_allocate(pol.handle, _i32(av), len(av), _i32(rq), len(rq), size, out, C.byref(res))
+    if rc < 0:
+        raise AllocatorError(rc, strerror(rc))
+    return list(out[:rc]), res.dict()

@@ -1,0 +1,506 @@
+// tp_abi.cu -- host side of the C ABI declared in include/tp_allocator.h.
+//
+// Mirrors the non-search parts of BestEffortPolicy.Allocate
+// (internal/pkg/allocator/besteffort_policy.go:88-151): the ordered validation checks,
+// the two short-circuits, filterPartitions' grouping and group order
+// (device.go:310-351), and the NodeId -> output order mapping (:141-148).  The search
+// itself (device.go:353-442 + the argmin) always runs on the GPU; there is no CPU path.
+#include <algorithm>
+#include <condition_variable>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "tp_kernels.cuh"
+
+typedef unsigned long long u64;
+
+namespace {
+
+struct Ctx { // one in-flight call: stream, events, pinned staging, device request + scratch
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    TpReq *h_req = nullptr; // pinned
+    TpReq *d_req = nullptr;
+    struct Out {
+        TpKey key;
+        u64 scored;
+    } *h_out = nullptr; // pinned
+    unsigned char *d_scratch = nullptr;
+    TpScratch scratch{};
+};
+
+// Everything the host derives from one request before (and after) the GPU search.
+struct Prep {
+    TpReq rq;
+    int status = 0;      // negative tp_status, or 0
+    int shortcut = 0;    // 1: return available as given; 2: return required as given
+    int n_req = 0;
+    bool family_only = false;
+};
+
+} // namespace
+
+struct tp_policy {
+    int n = 0, n_groups = 0;
+    std::vector<int32_t> node_id, group, parent_rank;
+    std::vector<uint8_t> weight;
+    bool weights_empty = true; // len(p2pWeights) == 0
+    int cuda_device = 0, sm_count = 148;
+    int kernel = 0;
+    u64 exhaustive_limit = 0;
+    uint8_t *d_weight = nullptr;
+    u64 *d_binom = nullptr;
+    u64 binom[TP_MAX_N + 1][TP_BINOM_COLS];
+    std::vector<Ctx> ctxs;
+    std::vector<int> free_ctx;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::string last_cuda_error;
+};
+
+namespace {
+
+#define TP_CUDA(p, call)                                                                      \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            std::lock_guard<std::mutex> lk__((p)->mu);                                        \
+            (p)->last_cuda_error = std::string(#call) + ": " + cudaGetErrorString(e__);       \
+            return TP_ERR_CUDA;                                                               \
+        }                                                                                     \
+    } while (0)
+
+struct DeviceGuard { // restores the caller's current device
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+    }
+    ~DeviceGuard() {
+        int cur = -1;
+        cudaGetDevice(&cur);
+        if (prev >= 0 && cur != prev) cudaSetDevice(prev);
+    }
+};
+
+struct CtxLease {
+    tp_policy *p;
+    int idx;
+    explicit CtxLease(tp_policy *pol) : p(pol) {
+        std::unique_lock<std::mutex> lk(p->mu);
+        p->cv.wait(lk, [&] { return !p->free_ctx.empty(); });
+        idx = p->free_ctx.back();
+        p->free_ctx.pop_back();
+    }
+    ~CtxLease() {
+        {
+            std::lock_guard<std::mutex> lk(p->mu);
+            p->free_ctx.push_back(idx);
+        }
+        p->cv.notify_one();
+    }
+    Ctx &ctx() { return p->ctxs[idx]; }
+};
+
+int init_ctx(tp_policy *p, Ctx &c) {
+    TP_CUDA(p, cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
+    TP_CUDA(p, cudaEventCreate(&c.ev0));
+    TP_CUDA(p, cudaEventCreate(&c.ev1));
+    TP_CUDA(p, cudaHostAlloc((void **)&c.h_req, sizeof(TpReq), cudaHostAllocDefault));
+    TP_CUDA(p, cudaHostAlloc((void **)&c.h_out, sizeof(Ctx::Out), cudaHostAllocDefault));
+    TP_CUDA(p, cudaMalloc((void **)&c.d_req, sizeof(TpReq)));
+    const size_t partial_bytes = sizeof(TpKey) * TP_MAX_BLOCKS;
+    const size_t total = partial_bytes + 64;
+    TP_CUDA(p, cudaMalloc((void **)&c.d_scratch, total));
+    TP_CUDA(p, cudaMemset(c.d_scratch, 0, total));
+    unsigned char *tail = c.d_scratch + partial_bytes;
+    c.scratch.partial = (TpKey *)c.d_scratch;
+    c.scratch.out = (TpKey *)tail;                    // 16 B
+    c.scratch.out_scored = (u64 *)(tail + 16);        // 8 B (contiguous with out: one D2H copy)
+    c.scratch.scored = (u64 *)(tail + 32);
+    c.scratch.ticket = (unsigned int *)(tail + 40);
+    return 0;
+}
+
+void free_ctx(Ctx &c) {
+    if (c.stream) cudaStreamDestroy(c.stream);
+    if (c.ev0) cudaEventDestroy(c.ev0);
+    if (c.ev1) cudaEventDestroy(c.ev1);
+    if (c.h_req) cudaFreeHost(c.h_req);
+    if (c.h_out) cudaFreeHost(c.h_out);
+    if (c.d_req) cudaFree(c.d_req);
+    if (c.d_scratch) cudaFree(c.d_scratch);
+}
+
+// The nine ordered checks and two short-circuits of Allocate (besteffort_policy.go:90-124),
+// then filterPartitions (device.go:310-351) as canonical order + group tables.
+void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
+             Prep &out) {
+    out.status = 0;
+    out.shortcut = 0;
+    out.n_req = n_req;
+    out.family_only = false;
+    if (size <= 0) { out.status = TP_ERR_INVALID_SIZE; return; }                   // :90-92
+    if (n_avail < size) { out.status = TP_ERR_INVALID_AVAILABLE; return; }         // :94-96
+    if (n_req > size) { out.status = TP_ERR_INVALID_REQUIRED; return; }            // :98-100
+    if (n_req > n_avail) { out.status = TP_ERR_INVALID_REQ_AVAILABLE; return; }    // :102-104
+    if (p->n == 0) { out.status = TP_ERR_INVALID_INIT; return; }                   // :106-108
+    if (n_avail == size) { out.shortcut = 1; return; }                             // :110-112
+    if (n_req == size) { out.shortcut = 2; return; }                               // :114-116
+    if (p->weights_empty) { out.status = TP_ERR_INVALID_INIT; return; }            // :118-120
+    if ((n_avail > 0 && !avail) || (n_req > 0 && !req)) { out.status = TP_ERR_BAD_ARGUMENT; return; }
+
+    // setContainsAll (:122-124) is evaluated on ids before any lookup; an index outside
+    // the policy is an id the reference's devicesMap does not know (it would nil-deref).
+    uint8_t state[TP_MAX_N] = {0}; // 1 available, 2 required
+    for (int i = 0; i < n_req; i++) {
+        bool found = false;
+        for (int j = 0; j < n_avail; j++)
+            if (avail[j] == req[i]) { found = true; break; }
+        if (!found) { out.status = TP_ERR_NO_CANDIDATE; return; }
+    }
+    for (int i = 0; i < n_avail; i++) {
+        if (avail[i] < 0 || avail[i] >= p->n || state[avail[i]]) { out.status = TP_ERR_BAD_INDEX; return; }
+        state[avail[i]] = 1;
+    }
+    for (int i = 0; i < n_req; i++) {
+        if (state[req[i]] == 2) { out.status = TP_ERR_BAD_INDEX; return; }
+        state[req[i]] = 2;
+    }
+
+    TpReq &rq = out.rq;
+    memset(&rq, 0, sizeof rq);
+    // free devices per group, NodeId ascending (device.go:322-333)
+    std::vector<std::vector<int>> members(p->n_groups);
+    for (int d = 0; d < p->n; d++)
+        if (state[d] == 1) members[p->group[d]].push_back(d);
+    std::vector<int> order;
+    for (int g = 0; g < p->n_groups; g++) {
+        if (members[g].empty()) continue;
+        std::sort(members[g].begin(), members[g].end(),
+                  [&](int a, int b) { return p->node_id[a] < p->node_id[b]; });
+        order.push_back(g);
+    }
+    // (free count, ParentId) ascending (device.go:342-349); group index breaks the ties the
+    // reference leaves to Go's map order.
+    std::sort(order.begin(), order.end(), [&](int a, int b) {
+        if (members[a].size() != members[b].size()) return members[a].size() < members[b].size();
+        if (p->parent_rank[a] != p->parent_rank[b]) return p->parent_rank[a] < p->parent_rank[b];
+        return a < b;
+    });
+    int n = 0;
+    for (size_t pos = 0; pos < order.size(); pos++) {
+        const std::vector<int> &m = members[order[pos]];
+        rq.gstart[pos] = (uint8_t)n;
+        rq.gsize[pos] = (uint8_t)m.size();
+        for (int d : m) {
+            rq.group_of[n] = (uint8_t)pos;
+            rq.canon[n++] = (uint8_t)d;
+        }
+    }
+    rq.n = n;
+    rq.k = size - n_req;
+    rq.n_groups = (int)order.size();
+    rq.n_req = n_req;
+    int dbits = 1;
+    while ((1 << dbits) < rq.n_groups) dbits++;
+    rq.dbits = dbits;
+    int c_req = 0;
+    for (int i = 0; i < n_req; i++) {
+        rq.req[i] = (uint8_t)req[i];
+        for (int j = 0; j < i; j++) c_req += p->weight[(size_t)req[j] * p->n + req[i]];
+    }
+    rq.c_req = c_req;
+    if (rq.k > n) { out.status = TP_ERR_NO_CANDIDATE; return; } // unreachable: n_avail > size
+    rq.total = rq.k <= TP_MAX_K ? p->binom[n][rq.k] : ~0ull; // saturating
+    const u64 limit = p->exhaustive_limit ? p->exhaustive_limit : (1ull << 38);
+    if (rq.k > TP_MAX_K || rq.total > limit || rq.k * dbits > TP_SIGMA_BITS) out.family_only = true;
+}
+
+// Winner key -> device indices in the reference's output order (besteffort_policy.go:141-148):
+// groups in sequence order, NodeId ascending inside a group, required last in request order.
+int decode(const Prep &pr, const TpKey &key, const int32_t *req, int32_t *out) {
+    const TpReq &rq = pr.rq;
+    if (key.hi == TP_KEY_INF_HI) return TP_ERR_NO_CANDIDATE;
+    const int m = tp_key_groups(key);
+    int remaining = rq.k, n_out = 0;
+    for (int i = 0; i < m; i++) {
+        const int g = (int)tp_key_get(key, i, rq.dbits);
+        if (g >= rq.n_groups) return TP_ERR_BAD_ARGUMENT;
+        const int take = std::min<int>(rq.gsize[g], remaining);
+        for (int t = 0; t < take; t++) out[n_out++] = rq.canon[rq.gstart[g] + t];
+        remaining -= take;
+    }
+    if (remaining != 0) return TP_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < pr.n_req; i++) out[n_out++] = req[i];
+    return n_out;
+}
+
+void shard_range(u64 total, int idx, int cnt, u64 &lo, u64 &hi) {
+    lo = (u64)(((unsigned __int128)total * (unsigned)idx) / (unsigned)cnt);
+    hi = (u64)(((unsigned __int128)total * (unsigned)(idx + 1)) / (unsigned)cnt);
+}
+
+// Upload the prepared request, run the search over shard (idx of cnt) `iters` times, fetch the key.
+int run_search(tp_policy *p, Ctx &c, const Prep &pr, int shard_idx, int shard_cnt, int iters, bool upload,
+               TpKey *key, tp_result *info, float *total_ms) {
+    if (pr.family_only) return TP_ERR_TOO_LARGE; // Family-only kernel: see tp_family (next milestone)
+    const TpReq &rq = pr.rq;
+    u64 lo, hi;
+    shard_range(rq.total, shard_idx, shard_cnt, lo, hi);
+    if (upload) {
+        *c.h_req = rq;
+        TP_CUDA(p, cudaMemcpyAsync(c.d_req, c.h_req, sizeof(TpReq), cudaMemcpyHostToDevice, c.stream));
+    }
+    TpLaunchInfo li{};
+    int launches = 0;
+    TP_CUDA(p, cudaEventRecord(c.ev0, c.stream));
+    for (int it = 0; it < iters; it++) {
+        if (hi > lo) {
+            TP_CUDA(p, tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, rq, lo, hi, c.scratch,
+                                                p->sm_count, c.stream, &li));
+            launches += li.launches;
+        }
+    }
+    TP_CUDA(p, cudaEventRecord(c.ev1, c.stream));
+    if (hi > lo) {
+        TP_CUDA(p, cudaMemcpyAsync(c.h_out, c.scratch.out, sizeof(Ctx::Out), cudaMemcpyDeviceToHost, c.stream));
+    } else {
+        c.h_out->key = TpKey{TP_KEY_INF_HI, TP_KEY_INF_HI};
+        c.h_out->scored = 0;
+    }
+    TP_CUDA(p, cudaStreamSynchronize(c.stream));
+    float ms = 0.f;
+    TP_CUDA(p, cudaEventElapsedTime(&ms, c.ev0, c.ev1));
+    if (total_ms) *total_ms = ms;
+    *key = c.h_out->key;
+    if (info) {
+        info->searched = 1;
+        info->kernel = TP_KERNEL_LEX;
+        info->subsets_scored = c.h_out->scored;
+        info->subsets_total = rq.total;
+        info->kernel_ms = ms / (iters > 0 ? iters : 1);
+        info->gpu_launches = launches;
+        info->key.hi = key->hi;
+        info->key.lo = key->lo;
+        if (key->hi != TP_KEY_INF_HI) {
+            info->score = tp_key_score(*key);
+            info->groups_touched = tp_key_groups(*key);
+        }
+    }
+    return 0;
+}
+
+} // namespace
+
+extern "C" {
+
+const char *tp_strerror(int status) {
+    switch (status) {
+    case TP_OK: return "ok";
+    // the reference's strings, besteffort_policy.go:36-43 and :73
+    case TP_ERR_INVALID_SIZE: return "allocation size can not be negative";
+    case TP_ERR_INVALID_AVAILABLE: return "available devices count less than allocation size";
+    case TP_ERR_INVALID_REQUIRED: return "must_include devices size is more than allocation size";
+    case TP_ERR_INVALID_REQ_AVAILABLE: return "must_include length should be less than or equal to avilable device size";
+    case TP_ERR_INVALID_INIT: return "Init method must be called before Allocate";
+    case TP_ERR_NO_CANDIDATE: return "No candidate subset found with matching criteria";
+    case TP_ERR_INIT_FAILED: return "Besteffort Policy init failed to initialize p2pWeights";
+    case TP_ERR_BAD_INDEX: return "unknown or duplicate device index";
+    case TP_ERR_BAD_ARGUMENT: return "bad argument";
+    case TP_ERR_TOO_LARGE: return "search space too large";
+    case TP_ERR_CUDA: return "CUDA error";
+    case TP_ERR_NCCL: return "NCCL error";
+    }
+    return "unknown status";
+}
+
+const char *tp_last_cuda_error(const tp_policy *p) { return p ? p->last_cuda_error.c_str() : ""; }
+
+int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
+    if (!t || !out) return TP_ERR_BAD_ARGUMENT;
+    *out = nullptr;
+    if (t->n_devices < 0 || t->n_devices > TP_MAX_N || t->n_groups < 0 || t->n_groups > t->n_devices)
+        return TP_ERR_BAD_ARGUMENT;
+    const int n = t->n_devices;
+    if (n > 0 && (!t->node_id || !t->group || !t->parent_rank || !t->weight)) return TP_ERR_BAD_ARGUMENT;
+    tp_policy *p = new (std::nothrow) tp_policy();
+    if (!p) return TP_ERR_BAD_ARGUMENT;
+    p->n = n;
+    p->n_groups = t->n_groups;
+    p->node_id.assign(t->node_id, t->node_id + n);
+    p->group.assign(t->group, t->group + n);
+    p->parent_rank.assign(t->parent_rank, t->parent_rank + t->n_groups);
+    p->weight.assign(t->weight, t->weight + (size_t)n * n);
+    for (int i = 0; i < n; i++)
+        if (p->group[i] < 0 || p->group[i] >= p->n_groups) { delete p; return TP_ERR_BAD_ARGUMENT; }
+    p->weights_empty = true;
+    for (uint8_t w : p->weight)
+        if (w) { p->weights_empty = false; break; }
+    // Init fails when no pair weight could be read (besteffort_policy.go:72-74)
+    if (n > 0 && p->weights_empty) { delete p; return TP_ERR_INIT_FAILED; }
+    for (int a = 0; a <= TP_MAX_N; a++)
+        for (int j = 0; j < TP_BINOM_COLS; j++) {
+            if (j == 0) p->binom[a][j] = 1;
+            else if (a == 0) p->binom[a][j] = 0;
+            else {
+                u64 s = p->binom[a - 1][j - 1] + p->binom[a - 1][j];
+                if (s < p->binom[a - 1][j]) s = ~0ull;
+                p->binom[a][j] = s;
+            }
+        }
+    p->kernel = o ? o->kernel : 0;
+    p->exhaustive_limit = o ? o->exhaustive_limit : 0;
+    int dev = o ? o->cuda_device : -1;
+    if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) { delete p; return TP_ERR_CUDA; }
+    p->cuda_device = dev;
+    int rc = [&]() -> int {
+        DeviceGuard guard(dev);
+        int sms = 0;
+        TP_CUDA(p, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        p->sm_count = sms > 0 ? sms : 148;
+        TP_CUDA(p, cudaMalloc((void **)&p->d_weight, std::max<size_t>((size_t)n * n, 16)));
+        TP_CUDA(p, cudaMemcpy(p->d_weight, p->weight.data(), (size_t)n * n, cudaMemcpyHostToDevice));
+        TP_CUDA(p, cudaMalloc((void **)&p->d_binom, sizeof(p->binom)));
+        TP_CUDA(p, cudaMemcpy(p->d_binom, p->binom, sizeof(p->binom), cudaMemcpyHostToDevice));
+        const int inflight = (o && o->max_inflight > 0) ? o->max_inflight : 8;
+        p->ctxs.resize(inflight);
+        for (int i = 0; i < inflight; i++) {
+            int r = init_ctx(p, p->ctxs[i]);
+            if (r) return r;
+            p->free_ctx.push_back(i);
+        }
+        return 0;
+    }();
+    if (rc) {
+        tp_destroy(p);
+        return rc;
+    }
+    *out = p;
+    return TP_OK;
+}
+
+void tp_destroy(tp_policy *p) {
+    if (!p) return;
+    {
+        DeviceGuard guard(p->cuda_device);
+        for (Ctx &c : p->ctxs) free_ctx(c);
+        if (p->d_weight) cudaFree(p->d_weight);
+        if (p->d_binom) cudaFree(p->d_binom);
+    }
+    delete p;
+}
+
+int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req,
+                int32_t size, int32_t *out, tp_result *info) {
+    if (!p || !out) return TP_ERR_BAD_ARGUMENT;
+    if (info) memset(info, 0, sizeof *info);
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr);
+    if (pr.status) return pr.status;
+    if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; } // :110-112, as given
+    if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }   // :114-116
+    DeviceGuard guard(p->cuda_device);
+    CtxLease lease(p);
+    TpKey key;
+    int rc = run_search(p, lease.ctx(), pr, 0, 1, 1, true, &key, info, nullptr);
+    if (rc) return rc;
+    return decode(pr, key, req, out);
+}
+
+int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, int32_t *out, int32_t out_stride,
+                      int32_t *status, tp_result *infos) {
+    if (!p || n_requests < 0 || (n_requests && (!rqs || !out || !status))) return TP_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < n_requests; i++) {
+        if (rqs[i].size > out_stride) { status[i] = TP_ERR_BAD_ARGUMENT; continue; }
+        status[i] = tp_allocate(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required,
+                                rqs[i].size, out + (size_t)i * out_stride, infos ? infos + i : nullptr);
+    }
+    return TP_OK;
+}
+
+int tp_search_resident(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req,
+                       int32_t size, int32_t shard_index, int32_t shard_count, int32_t iters, float *ms,
+                       tp_key *key, tp_result *info) {
+    if (!p || !key || shard_count <= 0 || shard_index < 0 || shard_index >= shard_count || iters <= 0)
+        return TP_ERR_BAD_ARGUMENT;
+    if (info) memset(info, 0, sizeof *info);
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr);
+    if (pr.status) return pr.status;
+    if (pr.shortcut) return 1;
+    DeviceGuard guard(p->cuda_device);
+    CtxLease lease(p);
+    Ctx &c = lease.ctx();
+    // upload first, outside the timed region
+    *c.h_req = pr.rq;
+    TP_CUDA(p, cudaMemcpyAsync(c.d_req, c.h_req, sizeof(TpReq), cudaMemcpyHostToDevice, c.stream));
+    TP_CUDA(p, cudaStreamSynchronize(c.stream));
+    TpKey k;
+    int rc = run_search(p, c, pr, shard_index, shard_count, iters, false, &k, info, ms);
+    if (rc) return rc;
+    key->hi = k.hi;
+    key->lo = k.lo;
+    return 0;
+}
+
+int tp_search_shard(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req,
+                    int32_t size, int32_t shard_index, int32_t shard_count, tp_key *key, tp_result *info) {
+    if (!p || !key || shard_count <= 0 || shard_index < 0 || shard_index >= shard_count) return TP_ERR_BAD_ARGUMENT;
+    if (info) memset(info, 0, sizeof *info);
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr);
+    if (pr.status) return pr.status;
+    if (pr.shortcut) return 1;
+    DeviceGuard guard(p->cuda_device);
+    CtxLease lease(p);
+    TpKey k;
+    int rc = run_search(p, lease.ctx(), pr, shard_index, shard_count, 1, true, &k, info, nullptr);
+    if (rc) return rc;
+    key->hi = k.hi;
+    key->lo = k.lo;
+    return 0;
+}
+
+int tp_decode(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req, int32_t size,
+              const tp_key *key, int32_t *out) {
+    if (!p || !key || !out) return TP_ERR_BAD_ARGUMENT;
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr);
+    if (pr.status) return pr.status;
+    if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; }
+    if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }
+    TpKey k{key->hi, key->lo};
+    return decode(pr, k, req, out);
+}
+
+int tp_build_weights(int32_t n, const int32_t *group, const int32_t *numa, const int32_t *link, uint8_t *out,
+                     int32_t cuda_device) {
+    if (n <= 0 || n > TP_MAX_N || !group || !numa || !link || !out) return TP_ERR_BAD_ARGUMENT;
+    int dev = cuda_device;
+    if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) return TP_ERR_CUDA;
+    DeviceGuard guard(dev);
+    int32_t *d_group = nullptr, *d_numa = nullptr, *d_link = nullptr;
+    uint8_t *d_out = nullptr;
+    const size_t nn = (size_t)n * n;
+    cudaError_t e = cudaMalloc((void **)&d_group, n * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_numa, n * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_link, nn * sizeof(int32_t));
+    if (e == cudaSuccess) e = cudaMalloc((void **)&d_out, nn);
+    if (e == cudaSuccess) e = cudaMemcpy(d_group, group, n * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_numa, numa, n * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_link, link, nn * sizeof(int32_t), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = tp_launch_build_weights(n, d_group, d_numa, d_link, d_out, 0);
+    if (e == cudaSuccess) e = cudaMemcpy(out, d_out, nn, cudaMemcpyDeviceToHost);
+    cudaFree(d_group);
+    cudaFree(d_numa);
+    cudaFree(d_link);
+    cudaFree(d_out);
+    return e == cudaSuccess ? TP_OK : TP_ERR_CUDA;
+}
+
+} // extern "C"

@@ -1,0 +1,91 @@
+// tp_common.cuh -- types shared by the host side of the C ABI and the sm_100a kernels.
+//
+// Vocabulary (follows the reference, internal/pkg/allocator/device.go):
+//   device     one KFD node with a render minor (a GPU or a partition), index 0..n-1
+//   group      the partitions of one physical GPU (DevicePartitions, device.go:75-80)
+//   free       available and not required (filterPartitions, device.go:310-351)
+//   canonical  order of the free devices: groups in filterPartitions order
+//              (fewest free first, then ParentId), NodeId ascending inside a group
+//   k'         size - len(required): how many free devices a candidate holds
+//   Family     the sets the reference's BFS can emit (device.go:375-440): per group
+//              nothing / the whole group / for at most one group a lowest-NodeId prefix
+//   RefKey     (m, sigma): groups touched, then whole groups ascending + the partial
+//              group: the order in which the BFS appends candidates
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "tp_allocator.h"
+
+#define TP_MAX_N TP_MAX_DEVICES
+#define TP_MAX_K TP_MAX_SUBSET
+#define TP_SIGMA_BITS 104 /* bits of the packed group sequence: 40 in key.hi + 64 in key.lo */
+
+// One prepared request, as the kernels read it (device resident, ~1 KB).
+struct TpReq {
+    int32_t n;        // free devices
+    int32_t k;        // k'
+    int32_t n_groups; // groups with at least one free device
+    int32_t n_req;    // required devices
+    int32_t dbits;    // bits per sigma digit = ceil(log2(n_groups)), >= 1
+    int32_t c_req;    // weight among the required devices (every pair once)
+    uint64_t total;   // C(n, k)
+    uint8_t canon[TP_MAX_N];    // canonical position -> device index
+    uint8_t group_of[TP_MAX_N]; // canonical position -> group position
+    uint8_t gstart[TP_MAX_N];   // group position -> first canonical position
+    uint8_t gsize[TP_MAX_N];    // group position -> free devices in the group
+    uint8_t req[TP_MAX_N];      // required device indices, request order
+};
+
+// 128-bit key, compared as (hi, lo); see tp_key in tp_allocator.h.
+struct TpKey {
+    unsigned long long hi, lo;
+};
+
+#define TP_KEY_INF_HI 0xFFFFFFFFFFFFFFFFull
+
+__host__ __device__ __forceinline__ bool tp_key_less(const TpKey &a, const TpKey &b) {
+    return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo);
+}
+
+// score:16 | m:8 | sigma digits, most significant first, dbits each, in a 104-bit field.
+__host__ __device__ __forceinline__ void tp_key_begin(TpKey &k, int score, int m) {
+    k.hi = ((unsigned long long)(unsigned)score << 48) | ((unsigned long long)(unsigned)m << 40);
+    k.lo = 0;
+}
+__host__ __device__ __forceinline__ void tp_key_put(TpKey &k, int i, int dbits, unsigned digit) {
+    int shift = TP_SIGMA_BITS - (i + 1) * dbits; // bit position inside the 104-bit field
+    if (shift >= 64) {
+        k.hi |= (unsigned long long)digit << (shift - 64);
+    } else if (shift + dbits <= 64) {
+        k.lo |= (unsigned long long)digit << shift;
+    } else { // straddles the two words
+        k.lo |= (unsigned long long)digit << shift;
+        k.hi |= (unsigned long long)digit >> (64 - shift);
+    }
+}
+__host__ __device__ __forceinline__ unsigned tp_key_get(const TpKey &k, int i, int dbits) {
+    int shift = TP_SIGMA_BITS - (i + 1) * dbits;
+    unsigned long long v;
+    if (shift >= 64)
+        v = k.hi >> (shift - 64);
+    else if (shift + dbits <= 64)
+        v = k.lo >> shift;
+    else
+        v = (k.lo >> shift) | (k.hi << (64 - shift));
+    return (unsigned)(v & ((1ull << dbits) - 1));
+}
+__host__ __device__ __forceinline__ int tp_key_score(const TpKey &k) { return (int)(k.hi >> 48); }
+__host__ __device__ __forceinline__ int tp_key_groups(const TpKey &k) { return (int)((k.hi >> 40) & 0xFF); }
+
+// Per-launch scratch in global memory: one partial winner per block, reduced by the
+// last block to finish (ticket), so one launch yields the final key with no second kernel.
+struct TpScratch {
+    TpKey *partial;               // [max_blocks]
+    unsigned long long *scored;   // running count of subsets scored
+    unsigned int *ticket;         // blocks finished
+    TpKey *out;                   // final key
+    unsigned long long *out_scored;
+};
+
+#define TP_MAX_BLOCKS 4096

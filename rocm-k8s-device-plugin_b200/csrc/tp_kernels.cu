@@ -1,0 +1,341 @@
+// tp_kernels.cu -- sm_100a kernels of the preferred-allocation search.
+//
+// Replaces the hot loops of the reference policy: getCandidateDeviceSubsets
+// (internal/pkg/allocator/device.go:353-442), addDeviceToSubsetAndUpdateWeight
+// (:254-273) and the argmin of BestEffortPolicy.Allocate (besteffort_policy.go:133-140).
+// Integer work only; the pair-weight matrix (<= 128 x 128 bytes) lives in shared memory,
+// so HBM traffic per request is the ~1 KB request descriptor and a 16-byte winner.
+#include "tp_kernels.cuh"
+
+typedef unsigned long long u64;
+
+// ---------------------------------------------------------------------------------------
+// Family membership + RefKey of one scored subset (slow path, reached only when a subset
+// scores no worse than the best Family member seen so far).  The subset arrives packed,
+// one canonical position per byte, ascending.
+// ---------------------------------------------------------------------------------------
+__device__ __noinline__ bool tp_family_key(u64 p0, u64 p1, int k, int score, int dbits,
+                                           const uint8_t *s_group, const uint8_t *s_gstart,
+                                           const uint8_t *s_gsize, TpKey &out) {
+    auto elem = [&](int i) { return (int)(((i < 8 ? p0 : p1) >> ((i & 7) * 8)) & 0xFF); };
+    TpKey key;
+    tp_key_begin(key, score, 0);
+    int n_whole = 0, m = 0, partial = -1, i = 0;
+    while (i < k) {
+        const int e = elem(i);
+        const int g = s_group[e];
+        int j = i + 1;
+        while (j < k && s_group[elem(j)] == g) j++;
+        const int cnt = j - i;
+        m++;
+        if (cnt == s_gsize[g]) {
+            tp_key_put(key, n_whole++, dbits, (unsigned)g);
+        } else {
+            if (partial >= 0) return false; // two partial groups: the BFS never emits this
+            if (e != s_gstart[g]) return false;
+            for (int t = 1; t < cnt; t++)
+                if (elem(i + t) != e + t) return false; // not the lowest-NodeId prefix
+            partial = g;
+        }
+        i = j;
+    }
+    if (partial >= 0) tp_key_put(key, n_whole, dbits, (unsigned)partial);
+    key.hi |= (u64)m << 40;
+    out = key;
+    return true;
+}
+
+__device__ __forceinline__ TpKey tp_warp_min_key(TpKey k) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+        TpKey o;
+        o.hi = __shfl_xor_sync(0xFFFFFFFFu, k.hi, off);
+        o.lo = __shfl_xor_sync(0xFFFFFFFFu, k.lo, off);
+        if (tp_key_less(o, k)) k = o;
+    }
+    return k;
+}
+
+// Block-wide min of the per-thread winners, then the cross-block step: every block stores
+// its partial, the last one to arrive (ticket) reduces all partials into scratch.out and
+// re-arms the scratch for the next launch.
+__device__ void tp_block_finish(TpKey best, u64 counted, const TpScratch &sc) {
+    __shared__ TpKey s_red[32];
+    __shared__ u64 s_cnt[32];
+    __shared__ bool s_last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    best = tp_warp_min_key(best);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) counted += __shfl_xor_sync(0xFFFFFFFFu, counted, off);
+    if (lane == 0) {
+        s_red[warp] = best;
+        s_cnt[warp] = counted;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+        u64 c = 0;
+        if (lane < nwarps) {
+            k = s_red[lane];
+            c = s_cnt[lane];
+        }
+        k = tp_warp_min_key(k);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
+        if (lane == 0) {
+            sc.partial[blockIdx.x] = k;
+            atomicAdd(sc.scored, c);
+            __threadfence();
+            const unsigned t = atomicAdd(sc.ticket, 1u);
+            s_last = (t == gridDim.x - 1);
+        }
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
+        TpKey o = sc.partial[i];
+        if (tp_key_less(o, k)) k = o;
+    }
+    k = tp_warp_min_key(k);
+    if (lane == 0) s_red[warp] = k;
+    __syncthreads();
+    if (warp == 0) {
+        TpKey f = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+        if (lane < nwarps) f = s_red[lane];
+        f = tp_warp_min_key(f);
+        if (lane == 0) {
+            *sc.out = f;
+            *sc.out_scored = atomicExch(sc.scored, 0ull);
+            *sc.ticket = 0u;
+        }
+    }
+}
+
+// Stage the request into shared memory: pair weights in canonical order, the unary term
+// u[x] = sum over required r of W[x][r], and the group tables.  Returns the seed bound:
+// the score of canonical positions {0..k-1}, which is always a Family member.
+struct TpSmem {
+    u64 *binom;       // [(n+1) * (K+1)]
+    uint16_t *u;      // [n]
+    uint8_t *w;       // [n * stride]
+    uint8_t *group, *gstart, *gsize;
+    int stride;
+};
+
+__device__ __forceinline__ TpSmem tp_smem_carve(unsigned char *smem, int n, int K) {
+    TpSmem s;
+    s.stride = (n + 3) & ~3;
+    s.binom = (u64 *)smem;
+    s.u = (uint16_t *)(s.binom + (n + 1) * (K + 1));
+    s.w = (uint8_t *)(s.u + ((n + 7) & ~7));
+    s.group = s.w + n * s.stride;
+    s.gstart = s.group + n;
+    s.gsize = s.gstart + n;
+    return s;
+}
+
+static size_t tp_smem_bytes(int n, int K) {
+    int stride = (n + 3) & ~3;
+    return (size_t)(n + 1) * (K + 1) * 8 + (size_t)((n + 7) & ~7) * 2 + (size_t)n * stride + 3 * (size_t)n + 16;
+}
+
+__device__ void tp_stage_request(const TpSmem &s, const uint8_t *__restrict__ W, int nd,
+                                 const u64 *__restrict__ binom_g, const TpReq *__restrict__ rq, int K,
+                                 int *s_bound) {
+    const int n = rq->n, tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < (n + 1) * (K + 1); i += nt) {
+        const int a = i / (K + 1), j = i - a * (K + 1);
+        s.binom[i] = binom_g[a * TP_BINOM_COLS + j];
+    }
+    for (int i = tid; i < n * n; i += nt) {
+        const int r = i / n, c = i - r * n;
+        s.w[r * s.stride + c] = (r == c) ? 0 : W[(int)rq->canon[r] * nd + rq->canon[c]];
+    }
+    for (int i = tid; i < n; i += nt) {
+        int u = 0;
+        for (int r = 0; r < rq->n_req; r++) u += W[(int)rq->canon[i] * nd + rq->req[r]];
+        s.u[i] = (uint16_t)u;
+        s.group[i] = rq->group_of[i];
+        s.gstart[i] = rq->gstart[i];
+        s.gsize[i] = rq->gsize[i];
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int sc = rq->c_req;
+        for (int i = 0; i < K; i++) {
+            sc += s.u[i];
+            for (int j = 0; j < i; j++) sc += s.w[j * s.stride + i];
+        }
+        *s_bound = sc;
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------------------------------
+// Kernel LEX: every thread owns a contiguous range of lexicographic ranks, unranks its
+// first subset from the binomial table, and walks.  The score of the first K-1 positions
+// is kept as prefix sums, so a step that only moves the last position costs K-1 byte
+// gathers from shared memory + K adds + one compare (the reference pays |S| map lookups
+// and two allocations per added device, device.go:254-273).
+// ---------------------------------------------------------------------------------------
+#define TP_LEX_THREADS 256
+
+template <int K>
+__global__ void __launch_bounds__(TP_LEX_THREADS)
+tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
+                  const TpReq *__restrict__ rq, u64 lo, u64 hi, u64 per_thread, TpScratch sc) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_bound;
+    const int n = rq->n;
+    const TpSmem s = tp_smem_carve(smem, n, K);
+    tp_stage_request(s, W, nd, binom_g, rq, K, &s_bound);
+    const int stride = s.stride, dbits = rq->dbits;
+
+    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+    u64 counted = 0;
+    const u64 gtid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    u64 my_lo = lo + gtid * per_thread;
+    if (my_lo < hi) {
+        u64 remaining = (hi - my_lo < per_thread) ? hi - my_lo : per_thread;
+        int c[K];
+        { // unrank my_lo in the lexicographic order of K-subsets of [0, n)
+            u64 r = my_lo;
+            int a = 0;
+#pragma unroll
+            for (int i = 0; i < K; i++) {
+                for (;; a++) {
+                    const u64 cnt = s.binom[(n - a - 1) * (K + 1) + (K - i - 1)];
+                    if (r < cnt) break;
+                    r -= cnt;
+                }
+                c[i] = a++;
+            }
+        }
+        int ps[K]; // ps[l] = c_req + score of positions 0..l-1
+        ps[0] = rq->c_req;
+        int level = 0;
+        int bound = s_bound;
+        while (remaining) {
+            int rowoff[K > 1 ? K - 1 : 1];
+#pragma unroll
+            for (int l = 0; l < K - 1; l++) {
+                rowoff[l] = c[l] * stride;
+                if (l >= level) {
+                    int add = s.u[c[l]];
+#pragma unroll
+                    for (int j = 0; j < l; j++) add += s.w[rowoff[j] + c[l]];
+                    ps[l + 1] = ps[l] + add;
+                }
+            }
+            const int base = ps[K - 1];
+            bound = min(bound, *(volatile int *)&s_bound);
+            int x = c[K - 1];
+            for (; x < n && remaining; ++x, --remaining) {
+                int sco = base + s.u[x];
+#pragma unroll
+                for (int j = 0; j < K - 1; j++) sco += s.w[rowoff[j] + x];
+                ++counted;
+                if (sco <= bound) {
+                    u64 p0 = 0, p1 = 0;
+#pragma unroll
+                    for (int j = 0; j < K - 1; j++) {
+                        if (j < 8) p0 |= (u64)c[j] << (8 * j);
+                        else p1 |= (u64)c[j] << (8 * (j - 8));
+                    }
+                    if constexpr (K - 1 < 8) p0 |= (u64)x << (8 * (K - 1));
+                    else p1 |= (u64)x << (8 * (K - 1 - 8));
+                    TpKey cand;
+                    if (tp_family_key(p0, p1, K, sco, dbits, s.group, s.gstart, s.gsize, cand)) {
+                        if (tp_key_less(cand, best)) best = cand;
+                        if (sco < bound) {
+                            bound = sco;
+                            atomicMin(&s_bound, sco);
+                        }
+                    }
+                }
+            }
+            if (!remaining) break;
+            // lexicographic successor of the prefix c[0..K-2]
+            int j = K - 2;
+#pragma unroll
+            for (int t = K - 2; t >= 0; --t)
+                if (j == t && c[t] == n - K + t) j = t - 1;
+            if (j < 0) break;
+#pragma unroll
+            for (int t = 0; t < K; t++) {
+                if (t == j) c[t]++;
+                else if (t > j) c[t] = c[t - 1] + 1;
+            }
+            level = j;
+        }
+    }
+    tp_block_finish(best, counted, sc);
+}
+
+template <int K>
+static cudaError_t launch_lex_k(const uint8_t *W, int nd, const u64 *binom, const TpReq *d_rq, const TpReq &h,
+                                u64 lo, u64 hi, const TpScratch &sc, int sm_count, cudaStream_t st,
+                                TpLaunchInfo *info) {
+    const u64 span = hi - lo;
+    const u64 max_threads = (u64)sm_count * 4 * TP_LEX_THREADS;
+    u64 per_thread = (span + max_threads - 1) / max_threads;
+    if (per_thread == 0) per_thread = 1;
+    u64 threads = (span + per_thread - 1) / per_thread;
+    int block = TP_LEX_THREADS;
+    if (threads < (u64)block) block = (int)((threads + 31) / 32 * 32);
+    if (block == 0) block = 32;
+    u64 blocks = (threads + block - 1) / block;
+    if (blocks == 0) blocks = 1;
+    if (blocks > TP_MAX_BLOCKS) { // cannot happen with sm_count*4 <= TP_MAX_BLOCKS; keep the scratch safe
+        blocks = TP_MAX_BLOCKS;
+        per_thread = (span + blocks * block - 1) / (blocks * block);
+    }
+    const size_t smem = tp_smem_bytes(h.n, K);
+    tp_exhaustive_lex<K><<<(unsigned)blocks, block, smem, st>>>(W, nd, binom, d_rq, lo, hi, per_thread, sc);
+    if (info) {
+        info->launches = 1;
+        info->blocks = (int)blocks;
+        info->threads = block;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t tp_launch_exhaustive_lex(const uint8_t *d_weight, int n_devices, const u64 *d_binom,
+                                     const TpReq *d_rq, const TpReq &h, u64 lo, u64 hi,
+                                     const TpScratch &sc, int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+#define TP_CASE(KK) \
+    case KK: return launch_lex_k<KK>(d_weight, n_devices, d_binom, d_rq, h, lo, hi, sc, sm_count, st, info);
+    switch (h.k) {
+        TP_CASE(1) TP_CASE(2) TP_CASE(3) TP_CASE(4) TP_CASE(5) TP_CASE(6) TP_CASE(7) TP_CASE(8)
+        TP_CASE(9) TP_CASE(10) TP_CASE(11) TP_CASE(12) TP_CASE(13) TP_CASE(14) TP_CASE(15) TP_CASE(16)
+    }
+#undef TP_CASE
+    return cudaErrorInvalidValue;
+}
+
+// ---------------------------------------------------------------------------------------
+// calculatePairWeight (device.go:135-157) for every pair at once.
+// ---------------------------------------------------------------------------------------
+__global__ void tp_build_weights_kernel(int n, const int32_t *__restrict__ group, const int32_t *__restrict__ numa,
+                                        const int32_t *__restrict__ link, uint8_t *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * n) return;
+    const int a = i / n, b = i - a * n;
+    const int ty = link[i];
+    int w = 0;
+    if (a != b && ty >= 0) {
+        w = (group[a] == group[b]) ? 10 : 20;        // sameDevIdWeight / differentDevIdWeight
+        w += (ty == 11) ? 10 : (ty == 2) ? 40 : 50;  // xgmi / pcie / other
+        w += (numa[a] == numa[b]) ? 10 : 20;         // sameNumaNodeWeight / differentNumaNodeWeight
+    }
+    out[i] = (uint8_t)w;
+}
+
+cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t *d_numa, const int32_t *d_link,
+                                    uint8_t *d_out, cudaStream_t st) {
+    const int total = n * n;
+    tp_build_weights_kernel<<<(total + 255) / 256, 256, 0, st>>>(n, d_group, d_numa, d_link, d_out);
+    return cudaGetLastError();
+}

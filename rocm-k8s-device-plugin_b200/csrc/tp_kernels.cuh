@@ -1,0 +1,27 @@
+// tp_kernels.cuh -- launcher interface between the C ABI (tp_abi.cu) and the kernels.
+#pragma once
+#include "tp_common.cuh"
+
+enum TpKernelId {
+    TP_KERNEL_AUTO = 0,
+    TP_KERNEL_LEX = 1,    // tp_exhaustive_lex: one rank range per thread, lexicographic walk
+    TP_KERNEL_FAMILY = 3, // tp_family: Family members only (search spaces too large to enumerate)
+};
+
+struct TpLaunchInfo {
+    int launches;
+    int blocks;
+    int threads;
+};
+
+// Score ranks [lo, hi) of the C(n, k') lexicographic subset order of request *rq (device
+// pointer; h_rq is the host copy used for launch geometry) and leave the winner in scratch.out.
+cudaError_t tp_launch_exhaustive_lex(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                     const TpReq *d_rq, const TpReq &h_rq, unsigned long long lo,
+                                     unsigned long long hi, const TpScratch &scratch, int sm_count,
+                                     cudaStream_t stream, TpLaunchInfo *info);
+
+cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t *d_numa, const int32_t *d_link,
+                                    uint8_t *d_out, cudaStream_t stream);
+
+#define TP_BINOM_COLS (TP_MAX_K + 1)

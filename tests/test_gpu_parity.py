@@ -1,0 +1,135 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle, bit-exact.
+
+Same request -> same ordered device ids and same score as the reference's policy
+(oracle/ref_policy.c), on the reference's own cases, the frozen golden vectors and
+seeded random requests over fixture and synthetic topologies."""
+import pytest
+
+import topo
+from __graft_entry__ import package
+from oracle.binding import RefPolicy
+
+pytestmark = pytest.mark.gpu
+tp = package()
+
+FIXTURES = ["mi308", "mi210", "cpx"]
+SYNTH = {"c4": topo.c4_topology, "hives": topo.hives_topology, "missing": topo.missing_links_topology,
+         "cpx64": topo.cpx64_topology}
+
+
+def make_pair(name):
+    devs, pairs = topo.fixture_topology(name) if name in FIXTURES else SYNTH[name]()
+    ref = RefPolicy()
+    ref.InitPairs(devs, pairs)
+    pol = tp.BestEffortPolicy(cuda_device=0)
+    pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+    return ref, pol
+
+
+@pytest.fixture(scope="module")
+def pols():
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            cache[name] = make_pair(name)
+        return cache[name]
+    yield get
+    for _, pol in cache.values():
+        pol.close()
+
+
+def check(ref, pol, av, rq, size):
+    want = ref.Allocate(av, rq, size)
+    got = pol.Allocate(av, rq, size)
+    assert got == want, (av, rq, size, got, want)
+    if ref.last["searched"]:
+        assert pol.last["searched"] == 1 and pol.last["gpu_launches"] >= 1
+        assert pol.last["score"] == ref.last["score"]
+        if pol.last["kernel"] != tp.KERNEL_FAMILY:
+            assert pol.last["subsets_scored"] == pol.last["subsets_total"]
+    else:
+        assert pol.last["searched"] == 0
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_reference_cases(pols, name):
+    """besteffort_policy_test.go:53-160 replayed on the GPU policy."""
+    ref, pol = pols(name)
+    for case in topo.golden("reference_cases.json")[name]:
+        if case["size"] > 12:
+            continue  # k=30 of 63: covered by the Family kernel tests
+        out = pol.Allocate(case["available"], case.get("required") or [], case["size"])
+        assert len(out) == case["size"]
+        if case.get("expected") is not None:
+            assert sorted(out) == sorted(case["expected"]), case["line"]
+        assert out == case["oracle"]["ids"]
+        assert pol.last["score"] == case["oracle"]["score"]
+
+
+def test_survey_vectors(pols):
+    for c in topo.golden("survey_cases.json"):
+        ref, pol = pols(c["topology"])
+        by_node = {d.NodeId: d.Id for d in ref.devices}
+        out = pol.Allocate([by_node[n] for n in c["available_nodes"]], [by_node[n] for n in c["required_nodes"]],
+                           c["size"])
+        assert out == c["oracle_ids"] and pol.last["score"] == c["score"]
+
+
+@pytest.mark.parametrize("name", FIXTURES)
+def test_frozen_random_cases(pols, name):
+    _, pol = pols(name)
+    for c in topo.golden("random_cases.json")[name]:
+        assert pol.Allocate(c["available"], c["required"], c["size"]) == c["ids"]
+        assert pol.last["score"] == c["score"]
+
+
+@pytest.mark.parametrize("name", FIXTURES + list(SYNTH))
+def test_random_requests_vs_oracle(pols, name):
+    ref, pol = pols(name)
+    ids = [d.Id for d in ref.devices]
+    gen = topo.SplitMix64(0xB200 ^ (len(name) << 8) ^ len(ids))
+    for _ in range(300):
+        av, rq, k = topo.random_request(gen, ids, kmax=7 if len(ids) > 40 else 8)
+        check(ref, pol, av, rq, k)
+
+
+def test_edge_cases(pols):
+    ref, pol = pols("cpx")
+    ids = [d.Id for d in ref.devices]
+    check(ref, pol, ids[:9], [], 8)            # one more available than requested
+    check(ref, pol, ids, ids[:7], 8)           # k' = 1
+    check(ref, pol, ids[:3], [], 3)            # short-circuit: available == size, order as given
+    check(ref, pol, list(reversed(ids[:5])), [ids[1], ids[0]], 2)  # short-circuit: required == size
+    check(ref, pol, ids[:20], [ids[19], ids[3]], 6)
+    for args, msg in [((ids, [], 0), "allocation size can not be negative"),
+                      ((ids[:2], [], 3), "available devices count less than allocation size"),
+                      ((ids, ids[:3], 2), "must_include devices size is more than allocation size"),
+                      ((ids[:6], ["amdgpu_xcp_60"], 3), "No candidate subset found with matching criteria")]:
+        with pytest.raises(tp.AllocatorError, match=msg):
+            pol.Allocate(*args)
+    with pytest.raises(tp.AllocatorError, match="unknown or duplicate device index"):
+        pol.Allocate(ids[:6] + ["nope"], ["nope"], 3)  # the reference nil-derefs here
+
+
+def test_full_size_cpx_8_of_63(pols):
+    """BASELINE config C3 at full size: 3 872 894 697 subsets, expected test1 + xcp_1..7 (score 840)."""
+    ref, pol = pols("cpx")
+    ids = [d.Id for d in ref.devices]
+    out = pol.Allocate(ids, [], 8)
+    assert out == ["test1"] + [f"amdgpu_xcp_{i}" for i in range(1, 8)]
+    assert pol.last["score"] == 840 and pol.last["subsets_scored"] == 3872894697
+
+
+def test_shards_cover_the_space(pols):
+    """Multi-GPU contract on one GPU: min over shard keys == the unsharded key, counts add up."""
+    ref, pol = pols("cpx")
+    ids = [d.Id for d in ref.devices]
+    gen = topo.SplitMix64(77)
+    for shards in (2, 3, 8):
+        av, rq, k = topo.random_request(gen, ids, kmax=6)
+        want = ref.Allocate(av, rq, k)
+        if not ref.last["searched"]:
+            continue
+        keys = [pol.SearchShard(av, rq, k, s, shards) for s in range(shards)]
+        assert pol.Decode(av, rq, k, min(keys)) == want
