@@ -1,0 +1,360 @@
+#!/usr/bin/env python
+"""bench.py -- subsets scored/sec of the GPU preferred-allocation search (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+Workload (all N): BASELINE config C4 -- synthetic 80-partition topology (10 GPUs x 8, 2 NUMA
+nodes, all XGMI), GetPreferredAllocation for 8 of 80 = C(80,8) = 28 987 537 150 subsets per
+step, sharded by rank range over the N GPUs (strong scaling), one min-all-reduce of the packed
+winner per step.  A step is one complete search; the result of every step is checked.
+
+  value     subsets/s with the request descriptor already in HBM (tp_prepare), the kernel (and,
+            for N>1, the NCCL min-all-reduce) timed with CUDA events on torch's current stream.
+  e2e       the same metric through the reference-facing call, BestEffortPolicy.Allocate with
+            host id strings: per step the H2D copy of the request and the D2H read of the winner
+            are inside the timed region.
+  roofline  integer-ALU roofline of the search kernel: achieved = subsets/s x
+            integer ops the kernel executes per subset; peak = IADD3 microbenchmark measured in
+            this run (MEASURED_PEAKS.json has no integer figure).  HBM traffic is ~1 KB/launch.
+  cpu_baseline  oracle/exhaustive.c (the same enumeration, all host threads) on a bounded
+            rank-range sample of the same workload.
+
+--impl reference times the reference side on the host cores: no Go toolchain exists in this
+image, so it is the C restatement (oracle/, kind "port"): the exhaustive scorer for the
+metric's unit, and the reference's own BFS policy latency for the same request beside it.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "subsets_scored_per_sec"
+UNIT = "subsets/s"
+WORKLOAD = "C4: synthetic 10x8-partition topology (80 devices), GetPreferredAllocation 8 of 80, C(80,8)=28987537150 subsets/step"
+
+
+def workload():
+    import topo
+    devs, pairs = topo.c4_topology()
+    ids = [d.Id for d in devs]
+    expected = ["test01"] + [f"amdgpu_xcp_{i}" for i in range(1, 8)]
+    return devs, pairs, ids, [], 8, expected, 840
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].startswith("Active")})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def percentile(xs, p):
+    xs = sorted(xs)
+    return xs[min(len(xs) - 1, int(p / 100.0 * len(xs)))]
+
+
+def cpu_exhaustive(ref, ids, req, size, seconds, threads=0):
+    """Time oracle/exhaustive.c on ranks [0, X) of the workload, X sized for ~`seconds`."""
+    probe = 1 << 28
+    t = time.perf_counter()
+    ref.AllocateExhaustive(ids, req, size, threads=threads, rank_lo=0, rank_hi=probe)
+    dt = time.perf_counter() - t
+    rate = ref.last["scored"] / dt
+    sample = int(min(max(rate * seconds, probe), ref.last["total"]))
+    t = time.perf_counter()
+    ref.AllocateExhaustive(ids, req, size, threads=threads, rank_lo=0, rank_hi=sample)
+    dt = time.perf_counter() - t
+    return ref.last["scored"] / dt, ref.last["threads"], ref.last["scored"], dt
+
+
+def run_reference(args, rank):
+    """--impl reference: the CPU side (oracle port; the Go reference cannot run here)."""
+    if rank != 0:
+        return
+    from oracle.binding import RefPolicy
+    devs, pairs, ids, req, size, expected, score = workload()
+    ref = RefPolicy()
+    ref.InitPairs(devs, pairs)
+    # the reference's own algorithm (BFS over partition groups) on this request
+    lat = []
+    for _ in range(200):
+        t = time.perf_counter()
+        out = ref.Allocate(ids, req, size)
+        lat.append((time.perf_counter() - t) * 1e6)
+    assert out == expected and ref.last["score"] == score
+    n_cand = ref.last["n_candidates"]
+    per_step_s = 4.0
+    for _ in range(args.warmup):
+        cpu_exhaustive(ref, ids, req, size, 0.5)
+    rates, scored, secs, threads = [], 0, 0.0, 1
+    for _ in range(args.steps):
+        r, threads, n, dt = cpu_exhaustive(ref, ids, req, size, per_step_s)
+        rates.append(r)
+        scored += n
+        secs += dt
+    value = scored / secs
+    sample = f"ranks [0, ~{scored // max(args.steps, 1)}) of C(80,8) per step, oracle/exhaustive.c"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(args.steps, 1) * 1e3,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32",
+            "data": "synthetic", "config": {"workload": WORKLOAD, "note": "bounded sample per step"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "reference_policy": {"what": "BFS restatement of BestEffortPolicy.Allocate (oracle/ref_policy.c), 1 thread",
+                                 "candidates_scored": n_cand, "p50_us": percentile(lat, 50),
+                                 "p99_us": percentile(lat, 99)},
+            "host_cores": os.cpu_count()}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="skip the C1/C2 latency and C3 legs")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank)
+
+    import torch
+    import torch.distributed as dist
+    from __graft_entry__ import package
+    tp = package()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the search has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
+
+    devs, pairs, ids, req, size, expected, score = workload()
+    pol = tp.BestEffortPolicy(cuda_device=local_rank)
+    pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    # ---- value: device-resident request, CUDA events on torch's current stream ----------
+    prep = tp.PreparedSearch(pol, ids, req, size, shard_index=rank, shard_count=world)
+    out = torch.zeros(3, dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream()
+    launches = 0
+
+    def step():
+        n = prep.launch(stream.cuda_stream, out.data_ptr())
+        if world > 1:  # the path's one exchange step: min of the packed (score, RefKey) winner
+            dist.all_reduce(out[0:1], op=dist.ReduceOp.MIN)
+        return n
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for e0, e1 in evs:
+        flush.fill_(1)  # L2 flush between timed iterations (untimed)
+        e0.record(stream)
+        launches += step()
+        e1.record(stream)
+    barrier()
+    dev_ms = max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in evs))
+    clocks = sampler.stop() if rank == 0 else None
+    key_hi = int(out[0].item())
+    scored = torch.tensor([int(out[2].item())], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(scored)
+    total_subsets = int(scored.item())
+    got = pol.Decode(ids, req, size, (key_hi, 0))
+    assert got == expected and (key_hi >> 48) == score, (got, key_hi)
+    assert total_subsets == 28987537150, total_subsets
+    value = total_subsets * args.steps / (dev_ms * 1e-3)
+
+    # ---- e2e: the reference-facing call, host buffers in, host ids out -------------------
+    h2d, d2h = 672, 24  # sizeof(TpReq) up, key + count down (csrc/tp_common.cuh, tp_abi.cu)
+
+    def e2e_step():
+        if world == 1:
+            return pol.Allocate(ids, req, size)
+        key = pol.SearchShard(ids, req, size, rank, world)
+        t = torch.tensor([key[0]], dtype=torch.int64).pin_memory().to(dev, non_blocking=True)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return pol.Decode(ids, req, size, (int(t.item()), 0))
+
+    for _ in range(min(args.warmup, 2)):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        res = e2e_step()
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    assert res == expected
+    e2e_value = 28987537150 * args.steps / e2e_s
+    if world > 1:
+        h2d, d2h = h2d + 8, d2h + 8
+
+    line = None
+    if rank == 0:
+        # ---- roofline of the dominant kernel (this rank's shard, kernel only) ------------
+        k_ms, _, info = tp.search_resident(pol, ids, req, size, iters=max(args.steps, 3), shard_index=rank,
+                                           shard_count=world)
+        k_ms /= max(args.steps, 3)
+        shard_subsets = prep.subsets
+        ops_per_subset = 9  # LEX kernel at k'=8: 7 weight gathers + u folded in = 8 integer adds + 1 compare
+        peak_iadd = tp.measure_int_peak(local_rank, 0)
+        peak_mix = tp.measure_int_peak(local_rank, 1)
+        achieved = shard_subsets * ops_per_subset / (k_ms * 1e-3) / 1e12
+        roofline = {"bound": "int32-alu", "achieved": achieved, "peak": peak_iadd / 1e3, "unit": "Tops/s",
+                    "frac": achieved / (peak_iadd / 1e3), "traffic": None,
+                    "peak_source": "IADD3 microbenchmark measured in this run (tp_measure_int_peak variant 0); "
+                                   "MEASURED_PEAKS.json has no integer figure",
+                    "peak_iadd3_plus_imad_tops": peak_mix / 1e3, "ops_per_subset": ops_per_subset,
+                    "kernel": "tp_exhaustive_lex<8>", "kernel_ms": k_ms,
+                    "kernel_subsets_per_s": shard_subsets / (k_ms * 1e-3),
+                    "north_star_15op_frac": shard_subsets * 15 / (k_ms * 1e-3) / 1e12 / (peak_iadd / 1e3),
+                    "hbm_bytes_per_launch_algorithmic": h2d + d2h}
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+                "config": {"workload": WORKLOAD, "sharding": f"rank-range x{world}, one NCCL min all-reduce/step"
+                           if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
+                           "kernel": "lex"},
+                "clocks": clocks,
+                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "ms_per_step": e2e_s / args.steps * 1e3, "api": "BestEffortPolicy.Allocate(ids, req, size)"},
+                "gpu_launches": launches, "roofline": roofline}
+        if world == 1 and not args.no_extra:
+            line["latency"] = latency_leg(tp, dev)
+            line["c3"] = c3_leg(tp)
+        if world == 1 and not args.no_cpu:
+            from oracle.binding import RefPolicy
+            ref = RefPolicy()
+            ref.InitPairs(devs, pairs)
+            r, threads, n, dt = cpu_exhaustive(ref, ids, req, size, 12.0)
+            line["cpu_baseline"] = {"value": r, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": f"ranks [0, {n}) of C(80,8) in {dt:.1f}s, oracle/exhaustive.c, "
+                                              f"{os.cpu_count()} host cpus visible"}
+    prep.close()
+    pol.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if line:
+        print(json.dumps(line))
+
+
+def latency_leg(tp, dev):
+    """p50/p99 GetPreferredAllocation latency on the latency-bound configs C1 and C2."""
+    import topo
+    from oracle.binding import RefPolicy
+    out = {}
+    for name, fixture, pick, size in (("c1_mi210_2of8", "mi210", None, 2),
+                                      ("c2_mesh_4of8", "cpx", [f"test{i}" for i in range(1, 9)], 4)):
+        devs, pairs = topo.fixture_topology(fixture)
+        ids = pick or [d.Id for d in devs]
+        pol = tp.BestEffortPolicy(cuda_device=dev.index)
+        pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+        ref = RefPolicy()
+        ref.InitPairs(devs, pairs)
+        want = ref.Allocate(ids, [], size)
+        av = pol.indices(ids)
+        for _ in range(200):
+            tp.allocate_indices(pol, av, [], size)
+        abi, host, cpu = [], [], []
+        for _ in range(3000):
+            t = time.perf_counter()
+            got_idx, info = tp.allocate_indices(pol, av, [], size)
+            abi.append((time.perf_counter() - t) * 1e6)
+        for _ in range(3000):
+            t = time.perf_counter()
+            got = pol.Allocate(ids, [], size)
+            host.append((time.perf_counter() - t) * 1e6)
+        assert got == want
+        for _ in range(3000):
+            t = time.perf_counter()
+            ref.Allocate(ids, [], size)
+            cpu.append((time.perf_counter() - t) * 1e6)
+        out[name] = {"subsets": info["subsets_total"], "c_abi_p50_us": percentile(abi, 50),
+                     "c_abi_p99_us": percentile(abi, 99), "policy_p50_us": percentile(host, 50),
+                     "policy_p99_us": percentile(host, 99), "kernel_us": info["kernel_ms"] * 1e3,
+                     "cpu_reference_bfs_p50_us": percentile(cpu, 50),
+                     "cpu_reference_candidates": ref.last["n_candidates"]}
+        pol.close()
+    out["note"] = "wall clock around the call (python ctypes overhead included in all three columns)"
+    return out
+
+
+def c3_leg(tp):
+    """BASELINE config C3: CPX fixture 8 of 63 (parity case) and 8 of 64 (the ~4.4e9 figure)."""
+    import topo
+    res = {}
+    for name, (devs, pairs), first in (("cpx_8of63", topo.fixture_topology("cpx"), "test1"),
+                                       ("cpx_8of64", topo.cpx64_topology(), "test1")):
+        ids = [d.Id for d in devs]
+        pol = tp.BestEffortPolicy(cuda_device=0)
+        pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+        tp.search_resident(pol, ids, [], 8, iters=1)
+        ms, key, info = tp.search_resident(pol, ids, [], 8, iters=5)
+        got = pol.Decode(ids, [], 8, key)
+        assert got[0] == first and info["score"] == 840, (got, info)
+        res[name] = {"subsets": info["subsets_total"], "kernel_ms": ms / 5,
+                     "subsets_per_s": info["subsets_total"] / (ms / 5 * 1e-3), "winner": got}
+        pol.close()
+    return res
+
+
+if __name__ == "__main__":
+    main()

@@ -145,6 +145,26 @@ int tp_search_resident(tp_policy *p, const int32_t *available, int32_t n_availab
                        int32_t n_required, int32_t size, int32_t shard_index, int32_t shard_count,
                        int32_t iters, float *ms, tp_key *key, tp_result *info);
 
+/* Stream-ordered form of tp_search_shard for callers that own the stream and the device
+ * memory (torch, NCCL): tp_prepare validates the request and uploads its descriptor;
+ * tp_launch enqueues the search on `cuda_stream` (a cudaStream_t) and leaves
+ *   d_out[0] = key.hi, d_out[1] = key.lo, d_out[2] = subsets scored
+ * in DEVICE memory d_out (3 x uint64), with no host synchronisation, so that a
+ * min-all-reduce of d_out[0] can be enqueued right behind it.  TP_KEY_NONE in d_out[0]
+ * means the shard holds no candidate.  One launch at a time per tp_prepared. */
+#define TP_KEY_NONE 0x7FFFFFFFFFFFFFFFull
+typedef struct tp_prepared tp_prepared;
+int tp_prepare(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+               int32_t n_required, int32_t size, int32_t shard_index, int32_t shard_count, tp_prepared **out);
+int tp_launch(tp_policy *p, tp_prepared *q, void *cuda_stream, uint64_t *d_out);
+uint64_t tp_prepared_subsets(const tp_prepared *q); /* subsets this shard scores per launch */
+void tp_prepared_free(tp_policy *p, tp_prepared *q);
+
+/* Roofline denominator: dependency-free integer-ALU microbenchmark on the given device.
+ * variant 0: IADD3 only (alu pipe); 1: IADD3 + IMAD mix (alu + fma pipes); 2: packed
+ * 16x2 min (VIMNMX).  *gops receives 10^9 lane-operations per second. */
+int tp_measure_int_peak(int32_t cuda_device, int32_t variant, double *gops);
+
 /* calculatePairWeight (device.go:135-157) for all pairs on the GPU: weight[i*n+j] from
  * per-device group / NUMA node and an n*n matrix of KFD link types (io_links/p2p_links
  * `type`; 11 = XGMI, 2 = PCIe; -1 = no link entry => weight 0, the Go map's zero value). */

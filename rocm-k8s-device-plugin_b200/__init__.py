@@ -117,6 +117,13 @@ def lib() -> C.CDLL:
     L.tp_search_resident.argtypes = req_args + [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float),
                                                 C.POINTER(TpKey), C.POINTER(TpResult)]
     L.tp_build_weights.argtypes = [C.c_int32, I32P, I32P, I32P, C.POINTER(C.c_uint8), C.c_int32]
+    L.tp_prepare.argtypes = req_args + [C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]
+    L.tp_launch.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.tp_prepared_subsets.restype = C.c_uint64
+    L.tp_prepared_subsets.argtypes = [C.c_void_p]
+    L.tp_prepared_free.argtypes = [C.c_void_p, C.c_void_p]
+    L.tp_prepared_free.restype = None
+    L.tp_measure_int_peak.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_double)]
     L.tph_new.restype = C.c_void_p
     L.tph_new.argtypes = [C.POINTER(TpOptions)]
     L.tph_free.argtypes = [C.c_void_p]
@@ -284,3 +291,41 @@ def allocate_indices(pol: BestEffortPolicy, av, rq, size):
     if rc < 0:
         raise AllocatorError(rc, strerror(rc))
     return list(out[:rc]), res.dict()
+
+
+class PreparedSearch:
+    """tp_prepare / tp_launch: stream-ordered search writing its key to caller-owned device memory."""
+
+    def __init__(self, pol: BestEffortPolicy, available, required, size, shard_index=0, shard_count=1):
+        self._pol = pol
+        av, rq = pol.indices(available), pol.indices(required or [])
+        q = C.c_void_p()
+        rc = lib().tp_prepare(pol.handle, _i32(av), len(av), _i32(rq), len(rq), size, shard_index, shard_count,
+                              C.byref(q))
+        if rc != 0:
+            raise AllocatorError(rc, strerror(rc) if rc < 0 else "request is answered by a short-circuit")
+        self._q = q
+        self.subsets = lib().tp_prepared_subsets(q)
+
+    def launch(self, cuda_stream: int, d_out_ptr: int) -> int:
+        """Enqueue on cuda_stream; d_out_ptr -> 3 x uint64 in device memory. Returns kernels launched."""
+        rc = lib().tp_launch(self._pol.handle, self._q, C.c_void_p(cuda_stream), C.c_void_p(d_out_ptr))
+        if rc < 0:
+            raise AllocatorError(rc, strerror(rc) + ": " + lib().tp_last_cuda_error(self._pol.handle).decode())
+        return rc
+
+    def close(self):
+        if getattr(self, "_q", None):
+            lib().tp_prepared_free(self._pol.handle, self._q)
+            self._q = None
+
+    __del__ = close
+
+
+def measure_int_peak(cuda_device=0, variant=0) -> float:
+    """10^9 integer lane-operations per second of the dependency-free microbenchmark."""
+    g = C.c_double()
+    rc = lib().tp_measure_int_peak(cuda_device, variant, C.byref(g))
+    if rc < 0:
+        raise AllocatorError(rc, strerror(rc))
+    return g.value

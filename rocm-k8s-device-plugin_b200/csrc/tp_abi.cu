@@ -478,6 +478,107 @@ int tp_decode(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t
     return decode(pr, k, req, out);
 }
 
+struct tp_prepared {
+    int ctx_idx;
+    Prep pr;
+    u64 lo, hi;
+};
+
+int tp_prepare(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req, int32_t size,
+               int32_t shard_index, int32_t shard_count, tp_prepared **out) {
+    if (!p || !out || shard_count <= 0 || shard_index < 0 || shard_index >= shard_count) return TP_ERR_BAD_ARGUMENT;
+    *out = nullptr;
+    tp_prepared *q = new (std::nothrow) tp_prepared();
+    if (!q) return TP_ERR_BAD_ARGUMENT;
+    prepare(p, avail, n_avail, req, n_req, size, q->pr);
+    int rc = q->pr.status ? q->pr.status : q->pr.shortcut ? 1 : q->pr.family_only ? TP_ERR_TOO_LARGE : 0;
+    if (rc) {
+        delete q;
+        return rc;
+    }
+    shard_range(q->pr.rq.total, shard_index, shard_count, q->lo, q->hi);
+    {
+        std::unique_lock<std::mutex> lk(p->mu);
+        p->cv.wait(lk, [&] { return !p->free_ctx.empty(); });
+        q->ctx_idx = p->free_ctx.back();
+        p->free_ctx.pop_back();
+    }
+    Ctx &c = p->ctxs[q->ctx_idx];
+    DeviceGuard guard(p->cuda_device);
+    *c.h_req = q->pr.rq;
+    cudaError_t e = cudaMemcpyAsync(c.d_req, c.h_req, sizeof(TpReq), cudaMemcpyHostToDevice, c.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
+    if (e != cudaSuccess) {
+        tp_prepared_free(p, q);
+        return TP_ERR_CUDA;
+    }
+    *out = q;
+    return TP_OK;
+}
+
+int tp_launch(tp_policy *p, tp_prepared *q, void *cuda_stream, uint64_t *d_out) {
+    if (!p || !q || !d_out) return TP_ERR_BAD_ARGUMENT;
+    Ctx &c = p->ctxs[q->ctx_idx];
+    DeviceGuard guard(p->cuda_device);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    TpScratch sc = c.scratch;
+    sc.out = (TpKey *)d_out;
+    sc.out_scored = (u64 *)(d_out + 2);
+    if (q->hi <= q->lo) { // empty shard: no candidate, nothing scored
+        static const u64 none[3] = {TP_KEY_INF_HI, TP_KEY_INF_HI, 0};
+        TP_CUDA(p, cudaMemcpyAsync(d_out, none, sizeof none, cudaMemcpyHostToDevice, st));
+        return 0;
+    }
+    TpLaunchInfo li{};
+    TP_CUDA(p, tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, q->pr.rq, q->lo, q->hi, sc,
+                                        p->sm_count, st, &li));
+    return li.launches;
+}
+
+uint64_t tp_prepared_subsets(const tp_prepared *q) { return q ? q->hi - q->lo : 0; }
+
+void tp_prepared_free(tp_policy *p, tp_prepared *q) {
+    if (!p || !q) return;
+    {
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->free_ctx.push_back(q->ctx_idx);
+    }
+    p->cv.notify_one();
+    delete q;
+}
+
+int tp_measure_int_peak(int32_t cuda_device, int32_t variant, double *gops) {
+    if (!gops) return TP_ERR_BAD_ARGUMENT;
+    int dev = cuda_device;
+    if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) return TP_ERR_CUDA;
+    DeviceGuard guard(dev);
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return TP_ERR_CUDA;
+    unsigned *d_out = nullptr;
+    cudaEvent_t e0, e1;
+    if (cudaMalloc((void **)&d_out, 64) != cudaSuccess) return TP_ERR_CUDA;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int blocks = sms * 8, iters = 1 << 14;
+    double best = 0;
+    cudaError_t e = tp_launch_int_peak(variant, blocks, 256, d_out, 0); // warm-up
+    for (int rep = 0; rep < 5 && e == cudaSuccess; rep++) {
+        cudaEventRecord(e0, 0);
+        e = tp_launch_int_peak(variant, blocks, iters, d_out, 0);
+        cudaEventRecord(e1, 0);
+        if (e == cudaSuccess) e = cudaEventSynchronize(e1);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double ops = 16.0 * 256.0 * blocks * iters;
+        if (ms > 0) best = std::max(best, ops / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d_out);
+    *gops = best;
+    return e == cudaSuccess ? TP_OK : TP_ERR_CUDA;
+}
+
 int tp_build_weights(int32_t n, const int32_t *group, const int32_t *numa, const int32_t *link, uint8_t *out,
                      int32_t cuda_device) {
     if (n <= 0 || n > TP_MAX_N || !group || !numa || !link || !out) return TP_ERR_BAD_ARGUMENT;

@@ -42,7 +42,9 @@ struct TpKey {
     unsigned long long hi, lo;
 };
 
-#define TP_KEY_INF_HI 0xFFFFFFFFFFFFFFFFull
+// "no candidate": larger than any real key (scores < 2^15) and still positive as int64, so a
+// signed 64-bit MIN all-reduce (ncclInt64 / torch.int64) orders it like the unsigned compare.
+#define TP_KEY_INF_HI 0x7FFFFFFFFFFFFFFFull
 
 __host__ __device__ __forceinline__ bool tp_key_less(const TpKey &a, const TpKey &b) {
     return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo);

@@ -339,3 +339,43 @@ cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t
     tp_build_weights_kernel<<<(total + 255) / 256, 256, 0, st>>>(n, d_group, d_numa, d_link, d_out);
     return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------------------
+// Integer-pipe microbenchmark (roofline denominator; MEASURED_PEAKS.json has no INT figure).
+// 16 independent accumulators per thread, no memory traffic; one "operation" = one 32-bit
+// lane result.  variant 0: IADD3 (alu pipe); 1: IADD3 + IMAD alternating (alu + fma pipes);
+// 2: packed 16x2 unsigned min.
+// ---------------------------------------------------------------------------------------
+template <int VARIANT>
+__global__ void __launch_bounds__(256) tp_int_peak_kernel(unsigned *out, unsigned seed, int iters) {
+    unsigned a[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) a[i] = seed * (i + 1) + threadIdx.x;
+    const unsigned b = seed | 1u, m = (seed >> 3) | 3u;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) {
+            if (VARIANT == 0) {
+                asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+            } else if (VARIANT == 1) {
+                if (i & 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(m), "r"(b));
+                else asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+            } else {
+                asm volatile("min.u16x2 %0, %0, %1;" : "+r"(a[i]) : "r"(b + i));
+            }
+        }
+    }
+    unsigned r = 0;
+#pragma unroll
+    for (int i = 0; i < 16; i++) r ^= a[i];
+    if (r == 0x12345678u) out[0] = r; // keep the chain alive without real traffic
+}
+
+cudaError_t tp_launch_int_peak(int variant, int blocks, int iters, unsigned *d_out, cudaStream_t st) {
+    switch (variant) {
+    case 0: tp_int_peak_kernel<0><<<blocks, 256, 0, st>>>(d_out, 12345u, iters); break;
+    case 1: tp_int_peak_kernel<1><<<blocks, 256, 0, st>>>(d_out, 12345u, iters); break;
+    default: tp_int_peak_kernel<2><<<blocks, 256, 0, st>>>(d_out, 12345u, iters); break;
+    }
+    return cudaGetLastError();
+}

@@ -25,3 +25,6 @@ cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t
                                     uint8_t *d_out, cudaStream_t stream);
 
 #define TP_BINOM_COLS (TP_MAX_K + 1)
+
+// 16 * 256 * blocks * iters lane-operations per launch.
+cudaError_t tp_launch_int_peak(int variant, int blocks, int iters, unsigned *d_out, cudaStream_t stream);
