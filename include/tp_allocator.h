@@ -47,6 +47,7 @@ typedef enum tp_status {
     TP_ERR_BAD_INDEX = -20,   /* unknown / duplicate device index (the reference nil-derefs, :61-68) */
     TP_ERR_BAD_ARGUMENT = -21,
     TP_ERR_TOO_LARGE = -22,   /* search space beyond what any kernel here enumerates */
+    TP_ERR_STATIC_SCRATCH = -23, /* tp_allocate_static: request needs more than the fixed scratch holds */
     TP_ERR_CUDA = -30,
     TP_ERR_NCCL = -31
 } tp_status;
@@ -159,6 +160,34 @@ int tp_prepare(tp_policy *p, const int32_t *available, int32_t n_available, cons
 int tp_launch(tp_policy *p, tp_prepared *q, void *cuda_stream, uint64_t *d_out);
 uint64_t tp_prepared_subsets(const tp_prepared *q); /* subsets this shard scores per launch */
 void tp_prepared_free(tp_policy *p, tp_prepared *q);
+
+/*
+ * tp_allocate without a tp_policy and without creating any memory.  (This entry point has no
+ * counterpart in the reference: the Go policy never leaves the host heap.)
+ *
+ * Meant for callers that cannot ask the CUDA runtime for memory when a request arrives: the
+ * plugin shares its GPU with tenant jobs, so HBM may already be full (cudaMalloc fails) and
+ * cudaMalloc/cudaFree wait for the device to go idle (they stall behind the tenants' kernels);
+ * the same holds for hosts confined to memory another runtime handed them.  The caller brings
+ *   topo       the host arrays of tp_create (read during the call only),
+ *   d_weight   topo->weight already in DEVICE memory (n_devices^2 bytes),
+ *   d_out      3 x uint64 of DEVICE memory: receives key.hi, key.lo, subsets scored,
+ *   out        host array, `size` device indices in the reference's output order,
+ * and the call makes no cudaMalloc, cudaFree, cudaHostAlloc, stream or event: its working
+ * memory is a fixed 36 KiB array compiled into the library (held by every GPU that loads it,
+ * until the process exits).  Consequences of that fixed array:
+ *   - limit: size - n_required <= TP_MAX_SUBSET and at most 2^38 candidate subsets; beyond
+ *     that the call returns TP_ERR_STATIC_SCRATCH and does no GPU work;
+ *   - the array is shared: calls whose GPU work overlaps on one device corrupt each other,
+ *     so run them one after another (the call itself blocks until its result is on the host);
+ *   - the first call on each GPU looks up the array's address and uploads a small constant
+ *     table, synchronising `cuda_stream`: make that first call before any stream capture.
+ * Runs on the CURRENT device, which must own d_weight, d_out and cuda_stream (a cudaStream_t,
+ * NULL for the default stream).  Same return values as tp_allocate otherwise.
+ */
+int tp_allocate_static(const tp_topology *topo, const uint8_t *d_weight, const int32_t *available,
+                       int32_t n_available, const int32_t *required, int32_t n_required, int32_t size,
+                       void *cuda_stream, uint64_t *d_out, int32_t *out, tp_result *info);
 
 /* Roofline denominator: dependency-free integer-ALU microbenchmark on the given device.
  * variant 0: IADD3 only (alu pipe); 1: IADD3 + IMAD mix (alu + fma pipes); 2: packed

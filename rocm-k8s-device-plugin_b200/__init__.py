@@ -124,6 +124,8 @@ def lib() -> C.CDLL:
     L.tp_prepared_free.argtypes = [C.c_void_p, C.c_void_p]
     L.tp_prepared_free.restype = None
     L.tp_measure_int_peak.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_double)]
+    L.tp_allocate_static.argtypes = [C.POINTER(TpTopology), C.c_void_p, I32P, C.c_int32, I32P, C.c_int32,
+                                     C.c_int32, C.c_void_p, C.c_void_p, I32P, C.POINTER(TpResult)]
     L.tph_new.restype = C.c_void_p
     L.tph_new.argtypes = [C.POINTER(TpOptions)]
     L.tph_free.argtypes = [C.c_void_p]

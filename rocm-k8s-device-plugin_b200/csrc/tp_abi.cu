@@ -313,6 +313,8 @@ const char *tp_strerror(int status) {
     case TP_ERR_BAD_INDEX: return "unknown or duplicate device index";
     case TP_ERR_BAD_ARGUMENT: return "bad argument";
     case TP_ERR_TOO_LARGE: return "search space too large";
+    case TP_ERR_STATIC_SCRATCH:
+        return "request does not fit the static scratch (more than 2^38 subsets, or size minus required above 16)";
     case TP_ERR_CUDA: return "CUDA error";
     case TP_ERR_NCCL: return "NCCL error";
     }
@@ -545,6 +547,73 @@ void tp_prepared_free(tp_policy *p, tp_prepared *q) {
     }
     p->cv.notify_one();
     delete q;
+}
+
+// tp_allocate for callers that may not allocate (see the long comment in tp_kernels.cu and the
+// declaration in tp_allocator.h).  Host-side preparation is the same code tp_allocate uses,
+// run on a throw-away, host-only policy object built from the caller's topology arrays.
+int tp_allocate_static(const tp_topology *t, const uint8_t *d_weight, const int32_t *avail, int32_t n_avail,
+                       const int32_t *req, int32_t n_req, int32_t size, void *cuda_stream, uint64_t *d_out,
+                       int32_t *out, tp_result *info) {
+    if (!t || !out) return TP_ERR_BAD_ARGUMENT;
+    if (info) memset(info, 0, sizeof *info);
+    const int n = t->n_devices;
+    if (n < 0 || n > TP_MAX_N || t->n_groups < 0 || t->n_groups > n) return TP_ERR_BAD_ARGUMENT;
+    if (n > 0 && (!t->node_id || !t->group || !t->parent_rank || !t->weight)) return TP_ERR_BAD_ARGUMENT;
+    tp_policy host; // host fields only: no stream, no device memory, never handed to tp_destroy
+    host.n = n;
+    host.n_groups = t->n_groups;
+    host.node_id.assign(t->node_id, t->node_id + n);
+    host.group.assign(t->group, t->group + n);
+    host.parent_rank.assign(t->parent_rank, t->parent_rank + t->n_groups);
+    host.weight.assign(t->weight, t->weight + (size_t)n * n);
+    for (int i = 0; i < n; i++)
+        if (host.group[i] < 0 || host.group[i] >= host.n_groups) return TP_ERR_BAD_ARGUMENT;
+    host.weights_empty = true;
+    for (uint8_t w : host.weight)
+        if (w) { host.weights_empty = false; break; }
+    for (int a = 0; a <= TP_MAX_N; a++)
+        for (int j = 0; j < TP_BINOM_COLS; j++) {
+            if (j == 0) host.binom[a][j] = 1;
+            else if (a == 0) host.binom[a][j] = 0;
+            else {
+                u64 s = host.binom[a - 1][j - 1] + host.binom[a - 1][j];
+                if (s < host.binom[a - 1][j]) s = ~0ull;
+                host.binom[a][j] = s;
+            }
+        }
+    Prep pr;
+    prepare(&host, avail, n_avail, req, n_req, size, pr);
+    if (pr.status) return pr.status;
+    if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; }
+    if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }
+    if (!d_weight || !d_out) return TP_ERR_BAD_ARGUMENT;
+    // The static array has room for a fixed number of block partials and this entry point only
+    // drives the exhaustive kernel: anything larger is refused, not silently truncated.
+    if (pr.family_only || pr.rq.total > TP_STATIC_MAX_SUBSETS) return TP_ERR_STATIC_SCRATCH;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    TpLaunchInfo li{};
+    cudaError_t e = tp_launch_exhaustive_lex_static(d_weight, n, &host.binom[0][0], pr.rq, 0, pr.rq.total,
+                                                    (unsigned long long *)d_out, st, &li);
+    u64 h_out[3] = {TP_KEY_INF_HI, TP_KEY_INF_HI, 0};
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_out, d_out, sizeof h_out, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    if (e != cudaSuccess) return TP_ERR_CUDA;
+    TpKey key{h_out[0], h_out[1]};
+    if (info) {
+        info->searched = 1;
+        info->kernel = TP_KERNEL_LEX;
+        info->subsets_scored = h_out[2];
+        info->subsets_total = pr.rq.total;
+        info->gpu_launches = li.launches;
+        info->key.hi = key.hi;
+        info->key.lo = key.lo;
+        if (key.hi != TP_KEY_INF_HI) {
+            info->score = tp_key_score(key);
+            info->groups_touched = tp_key_groups(key);
+        }
+    }
+    return decode(pr, key, req, out);
 }
 
 int tp_measure_int_peak(int32_t cuda_device, int32_t variant, double *gops) {

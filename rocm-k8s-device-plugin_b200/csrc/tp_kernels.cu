@@ -379,3 +379,91 @@ cudaError_t tp_launch_int_peak(int variant, int blocks, int iters, unsigned *d_o
     }
     return cudaGetLastError();
 }
+
+// ---------------------------------------------------------------------------------------
+// Static-scratch launch of the LEX search, behind tp_allocate_static (tp_allocator.h).
+//
+// Who this is for: a caller that is not allowed to create device memory when a request
+// arrives.  The device plugin runs beside tenant jobs on the very GPU it searches on; once a
+// tenant has filled HBM a cudaMalloc from the plugin fails, and even when it succeeds
+// cudaMalloc/cudaFree serialise against all work on the device, so they stall behind the
+// tenant's kernels.  Hosts that live entirely inside memory handed to them by another runtime
+// (a framework's tensor pool, a fixed arena set aside at boot) are in the same position.
+// Such a caller brings its own inputs (the weight matrix, in device memory) and its own
+// output slot; everything the search needs in between -- per-block partial winners, the
+// ticket and counter words, the request descriptor and the binomial table -- sits in the
+// array below, which is part of the loaded module: every GPU that loads this library holds
+// these TP_STATIC_SCRATCH_BYTES (36 KiB) until the process exits.
+//
+// The array is shared by all calls on a device and is never cleared for you by anyone else:
+// the words that must start at zero (ticket, counter) are zeroed on the caller's stream before
+// every launch, the rest is overwritten.  Two calls whose GPU work overlaps on one device
+// (different streams, different threads) would trample each other's partials -- serialise them.
+// ---------------------------------------------------------------------------------------
+#define TP_STATIC_MAX_BLOCKS 1024
+#define TP_STATIC_OFF_PARTIAL 0
+#define TP_STATIC_OFF_WORDS (TP_STATIC_MAX_BLOCKS * 16)          /* 64 B: scored, ticket */
+#define TP_STATIC_OFF_REQ (TP_STATIC_OFF_WORDS + 64)             /* TpReq, 672 B */
+#define TP_STATIC_OFF_BINOM (TP_STATIC_OFF_REQ + 768)            /* (TP_MAX_N+1) x TP_BINOM_COLS u64 */
+#define TP_STATIC_SCRATCH_BYTES 36864
+static_assert(sizeof(TpReq) <= 768, "request descriptor outgrew its slot");
+static_assert(TP_STATIC_OFF_BINOM + (TP_MAX_N + 1) * TP_BINOM_COLS * 8 <= TP_STATIC_SCRATCH_BYTES,
+              "static scratch too small");
+
+static __device__ __align__(256) unsigned char tp_static_scratch[TP_STATIC_SCRATCH_BYTES];
+
+#include <mutex>
+#define TP_STATIC_MAX_GPUS 64
+// In host code `tp_static_scratch` is only a handle for the runtime, not an address a kernel can
+// use; the device address is looked up once per GPU (with that GPU current) and kept here.
+static unsigned char *g_static_ptr[TP_STATIC_MAX_GPUS];
+static std::mutex g_static_mu;
+
+// First call on a device: resolve the array's device address and park the binomial table in
+// it.  Do this first call outside any stream capture (it synchronises the stream).
+static cudaError_t tp_static_setup(int dev, const u64 *h_binom, cudaStream_t st, unsigned char **out) {
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[dev]) {
+        unsigned char *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&ptr, tp_static_scratch);
+        if (e != cudaSuccess) return e;
+        e = cudaMemcpyAsync(ptr + TP_STATIC_OFF_BINOM, h_binom, (size_t)(TP_MAX_N + 1) * TP_BINOM_COLS * 8,
+                            cudaMemcpyHostToDevice, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e != cudaSuccess) return e;
+        g_static_ptr[dev] = ptr;
+    }
+    *out = g_static_ptr[dev];
+    return cudaSuccess;
+}
+
+// Runs on the CURRENT device.  d_weight and d_out belong to the caller; h_rq is copied into
+// the static array.  No cudaMalloc / cudaFree / stream, event or host-buffer creation here.
+cudaError_t tp_launch_exhaustive_lex_static(const uint8_t *d_weight, int n_devices, const u64 *h_binom,
+                                            const TpReq &h_rq, u64 lo, u64 hi, unsigned long long *d_out,
+                                            cudaStream_t st, TpLaunchInfo *info) {
+    int dev = -1, sms = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= TP_STATIC_MAX_GPUS) return cudaErrorInvalidDevice;
+    e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return e;
+    unsigned char *base = nullptr;
+    e = tp_static_setup(dev, h_binom, st, &base);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(base + TP_STATIC_OFF_WORDS, 0, 64, st); // ticket and counter start at zero
+    if (e != cudaSuccess) return e;
+    e = cudaMemcpyAsync(base + TP_STATIC_OFF_REQ, &h_rq, sizeof(TpReq), cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    TpScratch sc;
+    sc.partial = (TpKey *)(base + TP_STATIC_OFF_PARTIAL);
+    sc.scored = (u64 *)(base + TP_STATIC_OFF_WORDS);
+    sc.ticket = (unsigned int *)(base + TP_STATIC_OFF_WORDS + 8);
+    sc.out = (TpKey *)d_out;
+    sc.out_scored = d_out + 2;
+    // launch_lex_k uses at most 4 blocks per SM: capping the SM count keeps the grid within the
+    // TP_STATIC_MAX_BLOCKS partial slots on any GPU.
+    const int sm_cap = sms < TP_STATIC_MAX_BLOCKS / 4 ? sms : TP_STATIC_MAX_BLOCKS / 4;
+    return tp_launch_exhaustive_lex(d_weight, n_devices, (const u64 *)(base + TP_STATIC_OFF_BINOM),
+                                    (const TpReq *)(base + TP_STATIC_OFF_REQ), h_rq, lo, hi, sc, sm_cap, st, info);
+}

@@ -26,5 +26,13 @@ cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t
 
 #define TP_BINOM_COLS (TP_MAX_K + 1)
 
+// LEX search whose scratch is the library's file-scope __device__ array (see tp_kernels.cu):
+// current device, caller-owned d_weight / d_out, nothing allocated.
+#define TP_STATIC_MAX_SUBSETS (1ull << 38)
+cudaError_t tp_launch_exhaustive_lex_static(const uint8_t *d_weight, int n_devices,
+                                            const unsigned long long *h_binom, const TpReq &h_rq,
+                                            unsigned long long lo, unsigned long long hi,
+                                            unsigned long long *d_out, cudaStream_t stream, TpLaunchInfo *info);
+
 // 16 * 256 * blocks * iters lane-operations per launch.
 cudaError_t tp_launch_int_peak(int variant, int blocks, int iters, unsigned *d_out, cudaStream_t stream);

@@ -1,0 +1,111 @@
+"""tp_allocate_static: the entry point for callers that may not create device memory.
+
+A device plugin shares its GPU with tenant jobs: by the time a GetPreferredAllocation request
+arrives HBM can be full, and cudaMalloc / cudaFree stall behind whatever the tenants are
+running.  Such a caller hands in the weight matrix and a 24-byte output slot it already owns
+(here: two torch tensors made up front) and the library works out of a fixed array compiled
+into it.  The test drives that entry point through the C ABI and demands exactly what the
+regular entry point (tp_create + tp_allocate) returns -- same device indices in the same
+order, same score, same number of subsets scored -- on two calls in a row, because the
+second call finds the first call's leftovers in the shared array.
+
+This file sorts last on purpose: a run that stops at the first failure has then already run
+every other test.  It also passes when run on its own in a fresh process.
+"""
+import ctypes as C
+
+import pytest
+
+import topo
+from __graft_entry__ import package
+
+pytestmark = pytest.mark.gpu
+tp = package()
+
+
+def topology_arrays(devs, pairs):
+    """The index-based view tp_create takes (what the Go shim would build after Init)."""
+    n = len(devs)
+    group_of, parent = {}, []
+    group = []
+    for d in devs:
+        g = group_of.setdefault(d.DevId, len(group_of))
+        if g == len(parent):
+            parent.append("")
+        if "amdgpu_xcp" not in d.Id:
+            parent[g] = d.Id
+        group.append(g)
+    order = sorted(set(parent))
+    parent_rank = [order.index(p) for p in parent]
+    index_of = {d.NodeId: i for i, d in enumerate(devs)}
+    weight = [0] * (n * n)
+    for a, b, w in pairs:
+        i, j = index_of[a], index_of[b]
+        weight[i * n + j] = weight[j * n + i] = w
+    keep = {"node_id": (C.c_int32 * n)(*[d.NodeId for d in devs]), "group": (C.c_int32 * n)(*group),
+            "parent_rank": (C.c_int32 * len(parent))(*parent_rank), "weight": (C.c_uint8 * (n * n))(*weight)}
+    t = tp.TpTopology(n, len(parent), keep["node_id"], keep["group"], keep["parent_rank"], keep["weight"])
+    return t, keep, weight
+
+
+def i32(xs):
+    return (C.c_int32 * max(len(xs), 1))(*xs)
+
+
+def test_static_scratch_entry_matches_regular_entry_twice_in_a_row():
+    import torch
+    L = tp.lib()
+    torch.cuda.set_device(0)
+    devs, pairs = topo.fixture_topology("cpx")
+    t, keep, weight = topology_arrays(devs, pairs)
+    n = len(devs)
+
+    # the regular path: the library allocates its own device memory in tp_create
+    pol = C.c_void_p()
+    opts = tp.TpOptions(0, 0, 0, 0, 0)
+    assert L.tp_create(C.byref(t), C.byref(opts), C.byref(pol)) == 0
+
+    # what a no-allocation caller owns up front: weights and the output slot, in device memory
+    d_weight = torch.tensor(weight, dtype=torch.uint8, device="cuda:0")
+    d_out = torch.zeros(3, dtype=torch.int64, device="cuda:0")
+    torch.cuda.synchronize()
+    stream = torch.cuda.current_stream().cuda_stream
+
+    gen = topo.SplitMix64(0x57A71C)
+    requests = [(list(range(n)), [], 5),                       # 7 028 847 subsets, many blocks
+                (list(range(0, n, 2)), [4, 10], 6),            # required devices, k' = 4
+                (list(range(n)), [], 5)]                       # the first one again, on a used array
+    for _ in range(3):
+        av, rq, k = topo.random_request(gen, list(range(n)), kmax=6)
+        requests.append((av, rq, k))
+    searched = 0
+    for av, rq, k in requests:
+        want = i32([0] * k)
+        want_info = tp.TpResult()
+        rc_want = L.tp_allocate(pol, i32(av), len(av), i32(rq), len(rq), k, want, C.byref(want_info))
+        for attempt in range(2):  # two calls in a row on the same shared array
+            got = i32([-1] * k)
+            info = tp.TpResult()
+            rc = L.tp_allocate_static(C.byref(t), C.c_void_p(d_weight.data_ptr()), i32(av), len(av), i32(rq),
+                                      len(rq), k, C.c_void_p(stream), C.c_void_p(d_out.data_ptr()), got,
+                                      C.byref(info))
+            assert rc == rc_want == k, (rc, rc_want, tp.strerror(min(rc, 0)))
+            assert list(got[:k]) == list(want[:k]), (av, rq, k, attempt)      # bit-exact: integer indices
+            assert info.score == want_info.score and info.searched == want_info.searched
+            if info.searched:
+                searched += 1
+                assert info.subsets_scored == want_info.subsets_scored == want_info.subsets_total
+                assert (info.key.hi, info.key.lo) == (want_info.key.hi, want_info.key.lo)
+                host = d_out.cpu().tolist()  # the caller's own output slot holds the same key
+                assert (host[0], host[2]) == (info.key.hi, info.subsets_scored)
+    assert searched >= 6
+
+    # beyond the fixed scratch: refused with a status of its own, and no GPU work
+    devs80, pairs80 = topo.c4_topology()
+    t80, keep80, weight80 = topology_arrays(devs80, pairs80)
+    d_w80 = torch.tensor(weight80, dtype=torch.uint8, device="cuda:0")
+    got = i32([0] * 20)
+    rc = L.tp_allocate_static(C.byref(t80), C.c_void_p(d_w80.data_ptr()), i32(list(range(80))), 80, i32([]), 0, 20,
+                              C.c_void_p(stream), C.c_void_p(d_out.data_ptr()), got, None)
+    assert rc == -23 and "static scratch" in tp.strerror(rc)
+    L.tp_destroy(pol)
