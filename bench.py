@@ -253,25 +253,37 @@ def main():
                                            shard_count=world)
         k_ms /= max(args.steps, 3)
         shard_subsets = prep.subsets
-        ops_per_subset = 9  # LEX kernel at k'=8: 7 weight gathers + u folded in = 8 integer adds + 1 compare
-        peak_iadd = tp.measure_int_peak(local_rank, 0)
-        peak_mix = tp.measure_int_peak(local_rank, 1)
-        achieved = shard_subsets * ops_per_subset / (k_ms * 1e-3) / 1e12
-        roofline = {"bound": "int32-alu", "achieved": achieved, "peak": peak_iadd / 1e3, "unit": "Tops/s",
-                    "frac": achieved / (peak_iadd / 1e3), "traffic": None,
-                    "peak_source": "IADD3 microbenchmark measured in this run (tp_measure_int_peak variant 0); "
-                                   "MEASURED_PEAKS.json has no integer figure",
-                    "peak_iadd3_plus_imad_tops": peak_mix / 1e3, "ops_per_subset": ops_per_subset,
-                    "kernel": "tp_exhaustive_lex<8>", "kernel_ms": k_ms,
-                    "kernel_subsets_per_s": shard_subsets / (k_ms * 1e-3),
-                    "north_star_15op_frac": shard_subsets * 15 / (k_ms * 1e-3) / 1e12 / (peak_iadd / 1e3),
+        if info["kernel"] == tp.KERNEL_SPLIT:
+            h2d += 3352  # the work plan (TpPlan) travels with the request descriptor
+        peak_iadd = tp.measure_int_peak(local_rank, 0)      # IADD3, 32-bit lane-ops/s (x1e9)
+        peak_addmin = tp.measure_int_peak(local_rank, 3)    # VIADDMNMX.U16x2 lane-instr/s (x1e9)
+        rate = shard_subsets / (k_ms * 1e-3)
+        if info["kernel"] == tp.KERNEL_SPLIT:
+            # SPLIT executes one 16-bit add and one 16-bit min per subset (VIADDMNMX.U16x2: two
+            # subsets per lane-instruction); the peak is that instruction's measured rate x 4 ops.
+            ops_per_subset, kname, unit_note = 2, "tp_exhaustive_split<96,2>", "16-bit integer add/min ops"
+            peak_tops = peak_addmin * 4 / 1e3
+            peak_src = "VIADDMNMX.U16x2 microbenchmark in this run (tp_measure_int_peak variant 3) x 4 ops/lane-instr"
+        else:
+            # LEX at k'=8: 7 weight gathers + unary term = 8 integer adds + 1 compare per subset
+            ops_per_subset, kname, unit_note = 9, "tp_exhaustive_lex<8>", "32-bit integer ops"
+            peak_tops = peak_iadd / 1e3
+            peak_src = "IADD3 microbenchmark in this run (tp_measure_int_peak variant 0)"
+        achieved = rate * ops_per_subset / 1e12
+        roofline = {"bound": "int-alu", "achieved": achieved, "peak": peak_tops, "unit": "Tops/s",
+                    "frac": achieved / peak_tops, "traffic": None, "ops": unit_note,
+                    "peak_source": peak_src + "; MEASURED_PEAKS.json has no integer figure",
+                    "peak_iadd3_tops": peak_iadd / 1e3, "peak_viaddmnmx_u16x2_glane_instr": peak_addmin,
+                    "ops_per_subset": ops_per_subset, "kernel": kname, "kernel_ms": k_ms,
+                    "kernel_subsets_per_s": rate,
+                    "north_star_15op_frac": rate * 15 / 1e12 / (peak_iadd / 1e3),
                     "hbm_bytes_per_launch_algorithmic": h2d + d2h}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "sharding": f"rank-range x{world}, one NCCL min all-reduce/step"
                            if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
-                           "kernel": "lex"},
+                           "kernel": {1: "lex", 2: "split"}.get(info["kernel"], str(info["kernel"]))},
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": e2e_s / args.steps * 1e3, "api": "BestEffortPolicy.Allocate(ids, req, size)"},

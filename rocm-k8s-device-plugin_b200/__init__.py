@@ -29,7 +29,7 @@ STATUS = {
     "TP_ERR_INIT_FAILED": -7, "TP_ERR_BAD_INDEX": -20, "TP_ERR_BAD_ARGUMENT": -21, "TP_ERR_TOO_LARGE": -22,
     "TP_ERR_CUDA": -30, "TP_ERR_NCCL": -31,
 }
-KERNEL_AUTO, KERNEL_LEX, KERNEL_FAMILY = 0, 1, 3
+KERNEL_AUTO, KERNEL_LEX, KERNEL_SPLIT, KERNEL_FAMILY = 0, 1, 2, 3
 
 
 class TpKey(C.Structure):

@@ -12,7 +12,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libtpalloc.so")
 SOURCES = ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
-HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "host/besteffort_policy.h"]
+HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_split.cuh", "host/besteffort_policy.h"]
 NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "-Xcompiler", "-fPIC,-O3,-Wall", "-shared", "-cudart", "static"]
 

@@ -23,22 +23,26 @@ namespace {
 struct Ctx { // one in-flight call: stream, events, pinned staging, device request + scratch
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    TpReq *h_req = nullptr; // pinned
+    TpReq *h_req = nullptr; // pinned; a TpPlan follows it in the same buffer (h_plan / d_plan)
     TpReq *d_req = nullptr;
+    TpPlan *h_plan = nullptr, *d_plan = nullptr;
     struct Out {
         TpKey key;
         u64 scored;
     } *h_out = nullptr; // pinned
     unsigned char *d_scratch = nullptr;
     TpScratch scratch{};
+    unsigned *d_counter = nullptr; // work counter of kernel SPLIT (a word of d_scratch)
 };
 
 // Everything the host derives from one request before (and after) the GPU search.
 struct Prep {
     TpReq rq;
+    TpPlan plan;         // valid when kernel == TP_KERNEL_SPLIT
     int status = 0;      // negative tp_status, or 0
     int shortcut = 0;    // 1: return available as given; 2: return required as given
     int n_req = 0;
+    int kernel = TP_KERNEL_LEX;
     bool family_only = false;
 };
 
@@ -110,9 +114,12 @@ int init_ctx(tp_policy *p, Ctx &c) {
     TP_CUDA(p, cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking));
     TP_CUDA(p, cudaEventCreate(&c.ev0));
     TP_CUDA(p, cudaEventCreate(&c.ev1));
-    TP_CUDA(p, cudaHostAlloc((void **)&c.h_req, sizeof(TpReq), cudaHostAllocDefault));
+    static_assert(sizeof(TpReq) % 16 == 0, "the plan follows the request in one buffer");
+    TP_CUDA(p, cudaHostAlloc((void **)&c.h_req, sizeof(TpReq) + sizeof(TpPlan), cudaHostAllocDefault));
     TP_CUDA(p, cudaHostAlloc((void **)&c.h_out, sizeof(Ctx::Out), cudaHostAllocDefault));
-    TP_CUDA(p, cudaMalloc((void **)&c.d_req, sizeof(TpReq)));
+    TP_CUDA(p, cudaMalloc((void **)&c.d_req, sizeof(TpReq) + sizeof(TpPlan)));
+    c.h_plan = (TpPlan *)((unsigned char *)c.h_req + sizeof(TpReq));
+    c.d_plan = (TpPlan *)((unsigned char *)c.d_req + sizeof(TpReq));
     const size_t partial_bytes = sizeof(TpKey) * TP_MAX_BLOCKS;
     const size_t total = partial_bytes + 64;
     TP_CUDA(p, cudaMalloc((void **)&c.d_scratch, total));
@@ -123,6 +130,7 @@ int init_ctx(tp_policy *p, Ctx &c) {
     c.scratch.out_scored = (u64 *)(tail + 16);        // 8 B (contiguous with out: one D2H copy)
     c.scratch.scored = (u64 *)(tail + 32);
     c.scratch.ticket = (unsigned int *)(tail + 40);
+    c.d_counter = (unsigned *)(tail + 48);
     return 0;
 }
 
@@ -134,6 +142,70 @@ void free_ctx(Ctx &c) {
     if (c.h_out) cudaFreeHost(c.h_out);
     if (c.d_req) cudaFree(c.d_req);
     if (c.d_scratch) cudaFree(c.d_scratch);
+}
+
+// Work plan of kernel SPLIT for a prepared request (out.rq filled).  Returns false when the
+// request is outside what that kernel takes (k' < 4, too many positions per lane, scores that
+// would not fit its 16-bit packed arithmetic); the LEX kernel then serves it.
+bool build_plan(const tp_policy *p, Prep &out) {
+    const TpReq &rq = out.rq;
+    const int n = rq.n, k = rq.k;
+    if (k < 4 || k > TP_MAX_K) return false;
+    const int q = k >= 6 ? std::min(k - 4, TP_SPLIT_MAX_D + 2) : 2;
+    const int pp = k - q;
+    if (pp > TP_SPLIT_MAX_P || n - pp > TP_SPLIT_MAX_M || n - pp < q) return false;
+    int max_w = 0, max_u = 0;
+    for (int i = 0; i < n; i++) {
+        const uint8_t *row = &p->weight[(size_t)rq.canon[i] * p->n];
+        int u = 0;
+        for (int j = 0; j < n; j++) max_w = std::max<int>(max_w, row[rq.canon[j]]);
+        for (int r = 0; r < rq.n_req; r++) u += row[rq.req[r]];
+        max_u = std::max(max_u, u);
+    }
+    if (k * (k - 1) / 2 * max_w + k * max_u > TP_SPLIT_SCORE_LIMIT) return false;
+
+    TpPlan &pl = out.plan;
+    memset(&pl, 0, sizeof pl);
+    pl.p = pp;
+    pl.q = q;
+    pl.jt_hi = n - pp;
+    pl.n_entries = n - pp - q + 1;
+    const u64 cap0 = std::max<u64>(2048, rq.total >> 21);
+    u64 items = 0;
+    for (int e = 0; e < pl.n_entries; e++) {
+        const int jt = pl.jt_hi - e;
+        const u64 na = p->binom[n - 1 - jt][pp - 1];
+        const u64 chunks = (na + 31) / 32;
+        if (chunks == 0 || chunks > 0xFFFFFFFFull) return false;
+        int np = 1;
+        pl.cuts[e][0] = (uint8_t)(q - 1);
+        pl.cuts[e][1] = (uint8_t)jt;
+        if (q > 2) { // slices of the first walked position b0 in [q-1, jt), each about `cap` subsets per lane
+            u64 cap = std::max<u64>(cap0, (p->binom[jt][q] + TP_SPLIT_MAX_PIECES - 1) / TP_SPLIT_MAX_PIECES);
+            uint8_t desc[TP_SPLIT_MAX_PIECES + 1];
+            int nd = 0;
+            desc[nd++] = (uint8_t)jt;
+            u64 acc = 0;
+            for (int b0 = jt - 1; b0 >= q - 1; b0--) {
+                const u64 w = p->binom[b0][q - 1];
+                if (acc > 0 && acc + w > cap && nd < TP_SPLIT_MAX_PIECES) {
+                    desc[nd++] = (uint8_t)(b0 + 1);
+                    acc = 0;
+                }
+                acc += w;
+            }
+            desc[nd] = (uint8_t)(q - 1);
+            np = nd;
+            for (int i = 0; i <= nd; i++) pl.cuts[e][i] = desc[nd - i]; // ascending
+        }
+        pl.item_base[e] = (uint32_t)items;
+        pl.n_chunks[e] = (uint32_t)chunks;
+        pl.n_pieces[e] = (uint8_t)np;
+        items += chunks * (u64)np;
+        if (items > 0xFFFFFFF0ull) return false;
+    }
+    pl.total_items = (uint32_t)items;
+    return true;
 }
 
 // The nine ordered checks and two short-circuits of Allocate (besteffort_policy.go:90-124),
@@ -219,6 +291,8 @@ void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_
     rq.total = rq.k <= TP_MAX_K ? p->binom[n][rq.k] : ~0ull; // saturating
     const u64 limit = p->exhaustive_limit ? p->exhaustive_limit : (1ull << 38);
     if (rq.k > TP_MAX_K || rq.total > limit || rq.k * dbits > TP_SIGMA_BITS) out.family_only = true;
+    out.kernel = TP_KERNEL_LEX;
+    if (!out.family_only && p->kernel != TP_KERNEL_LEX && build_plan(p, out)) out.kernel = TP_KERNEL_SPLIT;
 }
 
 // Winner key -> device indices in the reference's output order (besteffort_policy.go:141-148):
@@ -245,29 +319,81 @@ void shard_range(u64 total, int idx, int cnt, u64 &lo, u64 &hi) {
     hi = (u64)(((unsigned __int128)total * (unsigned)(idx + 1)) / (unsigned)cnt);
 }
 
+// Stage request (and plan) in the call's pinned buffer and start the copy to the device.
+cudaError_t upload_request(Ctx &c, const Prep &pr) {
+    *c.h_req = pr.rq;
+    size_t bytes = sizeof(TpReq);
+    if (pr.kernel == TP_KERNEL_SPLIT) {
+        *c.h_plan = pr.plan;
+        bytes += sizeof(TpPlan);
+    }
+    return cudaMemcpyAsync(c.d_req, c.h_req, bytes, cudaMemcpyHostToDevice, c.stream);
+}
+
+// Does shard (idx of cnt) hold any work?  LEX shards by rank range, SPLIT by item stride.
+bool shard_nonempty(const Prep &pr, int idx, int cnt) {
+    if (pr.kernel == TP_KERNEL_SPLIT) return (u64)idx < pr.plan.total_items;
+    u64 lo, hi;
+    shard_range(pr.rq.total, idx, cnt, lo, hi);
+    return hi > lo;
+}
+
+// Subsets shard (idx of cnt) scores in one launch.
+u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
+    if (pr.kernel != TP_KERNEL_SPLIT) {
+        u64 lo, hi;
+        shard_range(pr.rq.total, idx, cnt, lo, hi);
+        return hi - lo;
+    }
+    if (cnt == 1) return pr.rq.total;
+    const TpPlan &pl = pr.plan;
+    const int n = pr.rq.n;
+    u64 sum = 0;
+    for (int e = 0; e < pl.n_entries; e++) {
+        const int jt = pl.jt_hi - e;
+        const u64 na = p->binom[n - 1 - jt][pl.p - 1];
+        for (int piece = 0; piece < pl.n_pieces[e]; piece++) {
+            const u64 per_lane = pl.q == 2 ? p->binom[jt][2]
+                                           : p->binom[pl.cuts[e][piece + 1]][pl.q] - p->binom[pl.cuts[e][piece]][pl.q];
+            for (u64 ac = 0; ac < pl.n_chunks[e]; ac++) {
+                const u64 item = pl.item_base[e] + (u64)piece * pl.n_chunks[e] + ac;
+                if (item % (unsigned)cnt != (unsigned)idx) continue;
+                sum += per_lane * std::min<u64>(32, na - ac * 32);
+            }
+        }
+    }
+    return sum;
+}
+
+// Enqueue the search kernel chosen by prepare() for shard (idx of cnt) on `st`, result into sc.out.
+cudaError_t launch_search(tp_policy *p, Ctx &c, const Prep &pr, int idx, int cnt, const TpScratch &sc,
+                          cudaStream_t st, TpLaunchInfo *li) {
+    if (pr.kernel == TP_KERNEL_SPLIT)
+        return tp_launch_exhaustive_split(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, c.d_plan, pr.plan, idx, cnt,
+                                          sc, c.d_counter, p->sm_count, st, li);
+    u64 lo, hi;
+    shard_range(pr.rq.total, idx, cnt, lo, hi);
+    return tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, lo, hi, sc, p->sm_count, st, li);
+}
+
 // Upload the prepared request, run the search over shard (idx of cnt) `iters` times, fetch the key.
 int run_search(tp_policy *p, Ctx &c, const Prep &pr, int shard_idx, int shard_cnt, int iters, bool upload,
                TpKey *key, tp_result *info, float *total_ms) {
     if (pr.family_only) return TP_ERR_TOO_LARGE; // Family-only kernel: see tp_family (next milestone)
     const TpReq &rq = pr.rq;
-    u64 lo, hi;
-    shard_range(rq.total, shard_idx, shard_cnt, lo, hi);
-    if (upload) {
-        *c.h_req = rq;
-        TP_CUDA(p, cudaMemcpyAsync(c.d_req, c.h_req, sizeof(TpReq), cudaMemcpyHostToDevice, c.stream));
-    }
+    const bool nonempty = shard_nonempty(pr, shard_idx, shard_cnt);
+    if (upload) TP_CUDA(p, upload_request(c, pr));
     TpLaunchInfo li{};
     int launches = 0;
     TP_CUDA(p, cudaEventRecord(c.ev0, c.stream));
     for (int it = 0; it < iters; it++) {
-        if (hi > lo) {
-            TP_CUDA(p, tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, rq, lo, hi, c.scratch,
-                                                p->sm_count, c.stream, &li));
+        if (nonempty) {
+            TP_CUDA(p, launch_search(p, c, pr, shard_idx, shard_cnt, c.scratch, c.stream, &li));
             launches += li.launches;
         }
     }
     TP_CUDA(p, cudaEventRecord(c.ev1, c.stream));
-    if (hi > lo) {
+    if (nonempty) {
         TP_CUDA(p, cudaMemcpyAsync(c.h_out, c.scratch.out, sizeof(Ctx::Out), cudaMemcpyDeviceToHost, c.stream));
     } else {
         c.h_out->key = TpKey{TP_KEY_INF_HI, TP_KEY_INF_HI};
@@ -280,7 +406,7 @@ int run_search(tp_policy *p, Ctx &c, const Prep &pr, int shard_idx, int shard_cn
     *key = c.h_out->key;
     if (info) {
         info->searched = 1;
-        info->kernel = TP_KERNEL_LEX;
+        info->kernel = pr.kernel;
         info->subsets_scored = c.h_out->scored;
         info->subsets_total = rq.total;
         info->kernel_ms = ms / (iters > 0 ? iters : 1);
@@ -439,8 +565,7 @@ int tp_search_resident(tp_policy *p, const int32_t *avail, int32_t n_avail, cons
     CtxLease lease(p);
     Ctx &c = lease.ctx();
     // upload first, outside the timed region
-    *c.h_req = pr.rq;
-    TP_CUDA(p, cudaMemcpyAsync(c.d_req, c.h_req, sizeof(TpReq), cudaMemcpyHostToDevice, c.stream));
+    TP_CUDA(p, upload_request(c, pr));
     TP_CUDA(p, cudaStreamSynchronize(c.stream));
     TpKey k;
     int rc = run_search(p, c, pr, shard_index, shard_count, iters, false, &k, info, ms);
@@ -483,7 +608,8 @@ int tp_decode(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t
 struct tp_prepared {
     int ctx_idx;
     Prep pr;
-    u64 lo, hi;
+    int shard_index, shard_count;
+    u64 subsets; // subsets this shard scores per launch
 };
 
 int tp_prepare(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req, int32_t size,
@@ -498,7 +624,9 @@ int tp_prepare(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_
         delete q;
         return rc;
     }
-    shard_range(q->pr.rq.total, shard_index, shard_count, q->lo, q->hi);
+    q->shard_index = shard_index;
+    q->shard_count = shard_count;
+    q->subsets = shard_subsets(p, q->pr, shard_index, shard_count);
     {
         std::unique_lock<std::mutex> lk(p->mu);
         p->cv.wait(lk, [&] { return !p->free_ctx.empty(); });
@@ -507,8 +635,7 @@ int tp_prepare(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_
     }
     Ctx &c = p->ctxs[q->ctx_idx];
     DeviceGuard guard(p->cuda_device);
-    *c.h_req = q->pr.rq;
-    cudaError_t e = cudaMemcpyAsync(c.d_req, c.h_req, sizeof(TpReq), cudaMemcpyHostToDevice, c.stream);
+    cudaError_t e = upload_request(c, q->pr);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c.stream);
     if (e != cudaSuccess) {
         tp_prepared_free(p, q);
@@ -526,18 +653,17 @@ int tp_launch(tp_policy *p, tp_prepared *q, void *cuda_stream, uint64_t *d_out) 
     TpScratch sc = c.scratch;
     sc.out = (TpKey *)d_out;
     sc.out_scored = (u64 *)(d_out + 2);
-    if (q->hi <= q->lo) { // empty shard: no candidate, nothing scored
+    if (!shard_nonempty(q->pr, q->shard_index, q->shard_count)) { // empty shard: no candidate, nothing scored
         static const u64 none[3] = {TP_KEY_INF_HI, TP_KEY_INF_HI, 0};
         TP_CUDA(p, cudaMemcpyAsync(d_out, none, sizeof none, cudaMemcpyHostToDevice, st));
         return 0;
     }
     TpLaunchInfo li{};
-    TP_CUDA(p, tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, q->pr.rq, q->lo, q->hi, sc,
-                                        p->sm_count, st, &li));
+    TP_CUDA(p, launch_search(p, c, q->pr, q->shard_index, q->shard_count, sc, st, &li));
     return li.launches;
 }
 
-uint64_t tp_prepared_subsets(const tp_prepared *q) { return q ? q->hi - q->lo : 0; }
+uint64_t tp_prepared_subsets(const tp_prepared *q) { return q ? q->subsets : 0; }
 
 void tp_prepared_free(tp_policy *p, tp_prepared *q) {
     if (!p || !q) return;
@@ -582,6 +708,7 @@ int tp_allocate_static(const tp_topology *t, const uint8_t *d_weight, const int3
                 host.binom[a][j] = s;
             }
         }
+    host.kernel = TP_KERNEL_LEX; // the static scratch is laid out for the LEX kernel only
     Prep pr;
     prepare(&host, avail, n_avail, req, n_req, size, pr);
     if (pr.status) return pr.status;

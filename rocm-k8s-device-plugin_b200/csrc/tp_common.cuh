@@ -91,3 +91,28 @@ struct TpScratch {
 };
 
 #define TP_MAX_BLOCKS 4096
+
+// ---- kernel SPLIT (tp_split.cuh): constants and the host-built work plan ----------------------
+#define TP_BIG 0x3000u
+#define TP_BIG2 0x30003000u
+#define TP_SPLIT_WARPS 8
+#define TP_SPLIT_THREADS (TP_SPLIT_WARPS * 32)
+#define TP_SPLIT_MAX_PIECES 16
+#define TP_SPLIT_MAX_P 12
+#define TP_SPLIT_MAX_D 4
+#define TP_SPLIT_SCORE_LIMIT 12000 /* every partial sum must stay below TP_BIG */
+
+// Work plan: items = (pivot, chunk of 32 lane sets, slice of the first walked position).
+struct TpPlan {
+    int32_t p, q;         // |A|, |B''| + 2
+    int32_t jt_hi;        // pivots run from jt_hi = n - p down to q
+    int32_t n_entries;    // jt_hi - q + 1
+    uint32_t total_items;
+    uint32_t reserved;
+    uint32_t item_base[TP_MAX_N]; // entry e <-> pivot jt_hi - e
+    uint32_t n_chunks[TP_MAX_N];  // chunks of 32 A's
+    uint8_t n_pieces[TP_MAX_N];
+    uint8_t cuts[TP_MAX_N][TP_SPLIT_MAX_PIECES + 1]; // first-B'' position slices [cuts[i], cuts[i+1])
+};
+
+

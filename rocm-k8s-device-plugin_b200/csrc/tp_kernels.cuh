@@ -5,6 +5,7 @@
 enum TpKernelId {
     TP_KERNEL_AUTO = 0,
     TP_KERNEL_LEX = 1,    // tp_exhaustive_lex: one rank range per thread, lexicographic walk
+    TP_KERNEL_SPLIT = 2,  // tp_exhaustive_split: lane sets x warp-uniform walk x unrolled pair nest
     TP_KERNEL_FAMILY = 3, // tp_family: Family members only (search spaces too large to enumerate)
 };
 
@@ -13,6 +14,14 @@ struct TpLaunchInfo {
     int blocks;
     int threads;
 };
+
+// Kernel SPLIT: shard s of P scores the plan's items s, s+P, ...; d_counter is a zeroable word
+// of scratch used to hand out items.  Needs n - plan.p <= TP_SPLIT_MAX_M.
+#define TP_SPLIT_MAX_M 96
+cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                       const TpReq *d_rq, const TpReq &h_rq, const TpPlan *d_plan,
+                                       const TpPlan &h_plan, int shard_idx, int shard_cnt, const TpScratch &scratch,
+                                       unsigned *d_counter, int sm_count, cudaStream_t stream, TpLaunchInfo *info);
 
 // Score ranks [lo, hi) of the C(n, k') lexicographic subset order of request *rq (device
 // pointer; h_rq is the host copy used for launch geometry) and leave the winner in scratch.out.

@@ -133,3 +133,36 @@ def test_shards_cover_the_space(pols):
             continue
         keys = [pol.SearchShard(av, rq, k, s, shards) for s in range(shards)]
         assert pol.Decode(av, rq, k, min(keys)) == want
+
+
+@pytest.mark.parametrize("name,sizes", [("mi308", range(4, 13)), ("cpx", (4, 5, 6, 7)), ("c4", (4, 5, 6)),
+                                        ("missing", range(4, 11)), ("hives", range(4, 12))])
+def test_split_kernel_all_depths(pols, name, sizes):
+    """Kernel SPLIT (k' >= 4): every walk depth D = 0..4 and both lane-vector widths (M = 64, 96),
+    LEX and SPLIT must agree with the oracle and with each other."""
+    ref, pol = pols(name)
+    devs = ref.devices
+    lex = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_LEX)
+    lex.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs],
+                        topo.fixture_topology(name)[1] if name in FIXTURES else SYNTH[name]()[1])
+    ids = [d.Id for d in devs]
+    gen = topo.SplitMix64(0x5B117 + len(ids))
+    seen = set()
+    for size in sizes:
+        for trial in range(4):
+            cap = 26 if size >= 9 else 40 if size >= 7 else len(ids)  # keep C(n,k') small enough for seconds
+            pool = ids[:] if trial == 0 and cap == len(ids) else [i for i in ids if gen.chance(0.6)][:cap]
+            if len(pool) <= size + 1:
+                pool = ids[:size + 3]
+            nreq = gen.below(3) if size > 5 else 0
+            req = pool[:nreq]
+            want = ref.Allocate(pool, req, size)
+            got = pol.Allocate(pool, req, size)
+            assert got == want, (name, size, pool, req)
+            assert pol.last["score"] == ref.last["score"]
+            assert pol.last["subsets_scored"] == pol.last["subsets_total"]
+            seen.add(pol.last["kernel"])
+            assert lex.Allocate(pool, req, size) == want and lex.last["kernel"] == tp.KERNEL_LEX
+            assert lex.last["key"] == pol.last["key"]
+    assert tp.KERNEL_SPLIT in seen
+    lex.close()
