@@ -143,8 +143,8 @@ def run_reference(args, rank):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the C1/C2 latency and C3 legs")
@@ -197,12 +197,12 @@ def main():
             dist.all_reduce(out[0:1], op=dist.ReduceOp.MIN)
         return n
 
-    for _ in range(args.warmup):
-        step()
-    barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    for _ in range(args.warmup):
+        step()
+    barrier()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     for e0, e1 in evs:
         flush.fill_(1)  # L2 flush between timed iterations (untimed)
@@ -211,7 +211,17 @@ def main():
         e1.record(stream)
     barrier()
     dev_ms = max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in evs))
+    # A search takes a few ms, far less than nvidia-smi's sampling period: keep the same kernel
+    # running (untimed) for ~1.5 s so that the clock / throttle record is taken under this load.
+    sustain = int(min(max(1500.0 / max(dev_ms / args.steps, 1e-3), 1), 5000))
+    t_s = time.perf_counter()
+    for _ in range(sustain):
+        step()
+    barrier()
+    sustain_ms = (time.perf_counter() - t_s) * 1e3
     clocks = sampler.stop() if rank == 0 else None
+    if clocks is not None:
+        clocks["sampled_over"] = f"warm-up + {args.steps} timed steps + {sustain} untimed steps of the same search ({sustain_ms:.0f} ms)"
     key_hi = int(out[0].item())
     scored = torch.tensor([int(out[2].item())], dtype=torch.int64, device=dev)
     if world > 1:

@@ -1,37 +1,68 @@
 """Build libtpalloc.so (the C ABI + sm_100a kernels) in-tree with nvcc.
 
 No torch, no JIT cache: the .so sits next to this file so that it travels to the GPU box
-with the repo snapshot.  `python build.py` or build() from __graft_entry__.
+with the repo snapshot.  Translation units are compiled in parallel (the SPLIT kernel is one
+unit per lane-vector width), then linked.  `python build.py [--force] [-v]`, or build() from
+__graft_entry__.
 """
 import os
 import subprocess
 import sys
+from concurrent.futures import ThreadPoolExecutor
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libtpalloc.so")
-SOURCES = ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
-HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_split.cuh", "host/besteffort_policy.h"]
-NVCC_FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
-              "-Xcompiler", "-fPIC,-O3,-Wall", "-shared", "-cudart", "static"]
+SOURCES = ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "csrc/tp_split_m64.cu", "csrc/tp_split_m96.cu",
+           "csrc/tp_split_m128.cu", "host/besteffort_policy.cpp"]
+HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_device.cuh", "csrc/tp_split.cuh",
+           "host/besteffort_policy.h"]
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall"] + ARCH
+INCLUDES = ["-I", os.path.join(ROOT, "include"), "-I", CSRC]
+
+
+def _deps():
+    return [os.path.join(HERE, f) for f in HEADERS] + [os.path.join(ROOT, "include", "tp_allocator.h")]
+
+
+def _obj(src):
+    return os.path.join(OBJ, os.path.basename(src).rsplit(".", 1)[0] + ".o")
+
+
+def _stale(target, sources):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(s) > t for s in sources if os.path.exists(s))
 
 
 def stale():
-    if not os.path.exists(LIB):
-        return True
-    t = os.path.getmtime(LIB)
-    deps = [os.path.join(HERE, f) for f in SOURCES + HEADERS] + [os.path.join(ROOT, "include", "tp_allocator.h")]
-    return any(os.path.getmtime(d) > t for d in deps if os.path.exists(d))
+    return _stale(LIB, [os.path.join(HERE, s) for s in SOURCES] + _deps())
+
+
+def _compile(src, force, verbose):
+    path, obj = os.path.join(HERE, src), _obj(src)
+    if not (force or _stale(obj, [path] + _deps())):
+        return ""
+    cmd = ["nvcc"] + CFLAGS + INCLUDES + ["-c", path, "-o", obj] + (["-Xptxas", "-v"] if verbose else [])
+    r = subprocess.run(cmd, capture_output=True, text=True, cwd=CSRC)
+    if r.returncode != 0:
+        raise RuntimeError(f"nvcc failed on {src}:\n{r.stdout}\n{r.stderr}")
+    return r.stdout + r.stderr
 
 
 def build(force=False, verbose=False):
     if not (force or stale()):
         return LIB
-    cmd = ["nvcc"] + NVCC_FLAGS + ["-I", os.path.join(ROOT, "include"), "-I", CSRC, "-o", LIB] \
-        + [os.path.join(HERE, s) for s in SOURCES]
+    os.makedirs(OBJ, exist_ok=True)
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 4)) as ex:
+        logs = list(ex.map(lambda s: _compile(s, force, verbose), SOURCES))
     if verbose:
-        cmd += ["-Xptxas", "-v"]
+        print("\n".join(logs))
+    cmd = ["nvcc", "-shared", "-cudart", "static"] + ARCH + ["-o", LIB] + [_obj(s) for s in SOURCES]
     subprocess.run(cmd, check=True, cwd=CSRC)
     return LIB
 

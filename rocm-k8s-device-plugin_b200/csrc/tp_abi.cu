@@ -154,11 +154,14 @@ bool build_plan(const tp_policy *p, Prep &out) {
     const int q = k >= 6 ? std::min(k - 4, TP_SPLIT_MAX_D + 2) : 2;
     const int pp = k - q;
     if (pp > TP_SPLIT_MAX_P || n - pp > TP_SPLIT_MAX_M || n - pp < q) return false;
-    int max_w = 0, max_u = 0;
+    int max_w = 0, max_u = 0, min_w = 255;
     for (int i = 0; i < n; i++) {
         const uint8_t *row = &p->weight[(size_t)rq.canon[i] * p->n];
         int u = 0;
-        for (int j = 0; j < n; j++) max_w = std::max<int>(max_w, row[rq.canon[j]]);
+        for (int j = 0; j < n; j++) {
+            max_w = std::max<int>(max_w, row[rq.canon[j]]);
+            if (j != i) min_w = std::min<int>(min_w, row[rq.canon[j]]);
+        }
         for (int r = 0; r < rq.n_req; r++) u += row[rq.req[r]];
         max_u = std::max(max_u, u);
     }
@@ -170,7 +173,11 @@ bool build_plan(const tp_policy *p, Prep &out) {
     pl.q = q;
     pl.jt_hi = n - pp;
     pl.n_entries = n - pp - q + 1;
-    const u64 cap0 = std::max<u64>(2048, rq.total >> 21);
+    pl.min_w = min_w;
+    // Slice so that there are >= ~16 items per resident warp (2 x 8 warps x 148 SMs) for the tail,
+    // while one item stays worth >= 4K subsets per lane so that the per-item set-up (unrank, lane
+    // vector: ~500 instructions) stays in the noise.
+    const u64 cap0 = std::min<u64>(std::max<u64>(4096, rq.total / 1200000), 32768);
     u64 items = 0;
     for (int e = 0; e < pl.n_entries; e++) {
         const int jt = pl.jt_hi - e;

@@ -108,7 +108,7 @@ struct TpPlan {
     int32_t jt_hi;        // pivots run from jt_hi = n - p down to q
     int32_t n_entries;    // jt_hi - q + 1
     uint32_t total_items;
-    uint32_t reserved;
+    int32_t min_w;        // smallest weight between two free devices
     uint32_t item_base[TP_MAX_N]; // entry e <-> pivot jt_hi - e
     uint32_t n_chunks[TP_MAX_N];  // chunks of 32 A's
     uint8_t n_pieces[TP_MAX_N];

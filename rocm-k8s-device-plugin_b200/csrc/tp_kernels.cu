@@ -7,171 +7,7 @@
 // so HBM traffic per request is the ~1 KB request descriptor and a 16-byte winner.
 #include "tp_kernels.cuh"
 
-typedef unsigned long long u64;
-
-// ---------------------------------------------------------------------------------------
-// Family membership + RefKey of one scored subset (slow path, reached only when a subset
-// scores no worse than the best Family member seen so far).  The subset arrives packed,
-// one canonical position per byte, ascending.
-// ---------------------------------------------------------------------------------------
-__device__ __noinline__ bool tp_family_key(u64 p0, u64 p1, int k, int score, int dbits,
-                                           const uint8_t *s_group, const uint8_t *s_gstart,
-                                           const uint8_t *s_gsize, TpKey &out) {
-    auto elem = [&](int i) { return (int)(((i < 8 ? p0 : p1) >> ((i & 7) * 8)) & 0xFF); };
-    TpKey key;
-    tp_key_begin(key, score, 0);
-    int n_whole = 0, m = 0, partial = -1, i = 0;
-    while (i < k) {
-        const int e = elem(i);
-        const int g = s_group[e];
-        int j = i + 1;
-        while (j < k && s_group[elem(j)] == g) j++;
-        const int cnt = j - i;
-        m++;
-        if (cnt == s_gsize[g]) {
-            tp_key_put(key, n_whole++, dbits, (unsigned)g);
-        } else {
-            if (partial >= 0) return false; // two partial groups: the BFS never emits this
-            if (e != s_gstart[g]) return false;
-            for (int t = 1; t < cnt; t++)
-                if (elem(i + t) != e + t) return false; // not the lowest-NodeId prefix
-            partial = g;
-        }
-        i = j;
-    }
-    if (partial >= 0) tp_key_put(key, n_whole, dbits, (unsigned)partial);
-    key.hi |= (u64)m << 40;
-    out = key;
-    return true;
-}
-
-__device__ __forceinline__ TpKey tp_warp_min_key(TpKey k) {
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-        TpKey o;
-        o.hi = __shfl_xor_sync(0xFFFFFFFFu, k.hi, off);
-        o.lo = __shfl_xor_sync(0xFFFFFFFFu, k.lo, off);
-        if (tp_key_less(o, k)) k = o;
-    }
-    return k;
-}
-
-// Block-wide min of the per-thread winners, then the cross-block step: every block stores
-// its partial, the last one to arrive (ticket) reduces all partials into scratch.out and
-// re-arms the scratch for the next launch.
-__device__ void tp_block_finish(TpKey best, u64 counted, const TpScratch &sc) {
-    __shared__ TpKey s_red[32];
-    __shared__ u64 s_cnt[32];
-    __shared__ bool s_last;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
-    best = tp_warp_min_key(best);
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) counted += __shfl_xor_sync(0xFFFFFFFFu, counted, off);
-    if (lane == 0) {
-        s_red[warp] = best;
-        s_cnt[warp] = counted;
-    }
-    __syncthreads();
-    if (warp == 0) {
-        TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
-        u64 c = 0;
-        if (lane < nwarps) {
-            k = s_red[lane];
-            c = s_cnt[lane];
-        }
-        k = tp_warp_min_key(k);
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
-        if (lane == 0) {
-            sc.partial[blockIdx.x] = k;
-            atomicAdd(sc.scored, c);
-            __threadfence();
-            const unsigned t = atomicAdd(sc.ticket, 1u);
-            s_last = (t == gridDim.x - 1);
-        }
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
-    for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
-        TpKey o = sc.partial[i];
-        if (tp_key_less(o, k)) k = o;
-    }
-    k = tp_warp_min_key(k);
-    if (lane == 0) s_red[warp] = k;
-    __syncthreads();
-    if (warp == 0) {
-        TpKey f = {TP_KEY_INF_HI, TP_KEY_INF_HI};
-        if (lane < nwarps) f = s_red[lane];
-        f = tp_warp_min_key(f);
-        if (lane == 0) {
-            *sc.out = f;
-            *sc.out_scored = atomicExch(sc.scored, 0ull);
-            *sc.ticket = 0u;
-        }
-    }
-}
-
-// Stage the request into shared memory: pair weights in canonical order, the unary term
-// u[x] = sum over required r of W[x][r], and the group tables.  Returns the seed bound:
-// the score of canonical positions {0..k-1}, which is always a Family member.
-struct TpSmem {
-    u64 *binom;       // [(n+1) * (K+1)]
-    uint16_t *u;      // [n]
-    uint8_t *w;       // [n * stride]
-    uint8_t *group, *gstart, *gsize;
-    int stride;
-};
-
-__device__ __forceinline__ TpSmem tp_smem_carve(unsigned char *smem, int n, int K) {
-    TpSmem s;
-    s.stride = (n + 3) & ~3;
-    s.binom = (u64 *)smem;
-    s.u = (uint16_t *)(s.binom + (n + 1) * (K + 1));
-    s.w = (uint8_t *)(s.u + ((n + 7) & ~7));
-    s.group = s.w + n * s.stride;
-    s.gstart = s.group + n;
-    s.gsize = s.gstart + n;
-    return s;
-}
-
-static __host__ __device__ size_t tp_smem_bytes(int n, int K) {
-    int stride = (n + 3) & ~3;
-    return (size_t)(n + 1) * (K + 1) * 8 + (size_t)((n + 7) & ~7) * 2 + (size_t)n * stride + 3 * (size_t)n + 16;
-}
-
-__device__ void tp_stage_request(const TpSmem &s, const uint8_t *__restrict__ W, int nd,
-                                 const u64 *__restrict__ binom_g, const TpReq *__restrict__ rq, int K,
-                                 int *s_bound) {
-    const int n = rq->n, tid = threadIdx.x, nt = blockDim.x;
-    for (int i = tid; i < (n + 1) * (K + 1); i += nt) {
-        const int a = i / (K + 1), j = i - a * (K + 1);
-        s.binom[i] = binom_g[a * TP_BINOM_COLS + j];
-    }
-    for (int i = tid; i < n * n; i += nt) {
-        const int r = i / n, c = i - r * n;
-        s.w[r * s.stride + c] = (r == c) ? 0 : W[(int)rq->canon[r] * nd + rq->canon[c]];
-    }
-    for (int i = tid; i < n; i += nt) {
-        int u = 0;
-        for (int r = 0; r < rq->n_req; r++) u += W[(int)rq->canon[i] * nd + rq->req[r]];
-        s.u[i] = (uint16_t)u;
-        s.group[i] = rq->group_of[i];
-        s.gstart[i] = rq->gstart[i];
-        s.gsize[i] = rq->gsize[i];
-    }
-    __syncthreads();
-    if (tid == 0) {
-        int sc = rq->c_req;
-        for (int i = 0; i < K; i++) {
-            sc += s.u[i];
-            for (int j = 0; j < i; j++) sc += s.w[j * s.stride + i];
-        }
-        *s_bound = sc;
-    }
-    __syncthreads();
-}
+#include "tp_device.cuh"
 
 // ---------------------------------------------------------------------------------------
 // Kernel LEX: every thread owns a contiguous range of lexicographic ranks, unranks its
@@ -315,7 +151,23 @@ cudaError_t tp_launch_exhaustive_lex(const uint8_t *d_weight, int n_devices, con
     return cudaErrorInvalidValue;
 }
 
-#include "tp_split.cuh"
+// Kernel SPLIT: pick the narrowest lane vector that holds every pivot (n - p positions).
+cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, const u64 *d_binom,
+                                       const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, const TpPlan &hp,
+                                       int shard_idx, int shard_cnt, const TpScratch &sc, unsigned *d_counter,
+                                       int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+    const int D = hp.q - 2, need = h.n - hp.p;
+    if (need <= 64)
+        return tp_launch_split_m64(D, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc,
+                                   d_counter, sm_count, st, info);
+    if (need <= 96)
+        return tp_launch_split_m96(D, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc,
+                                   d_counter, sm_count, st, info);
+    if (need <= 128)
+        return tp_launch_split_m128(D, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc,
+                                    d_counter, sm_count, st, info);
+    return cudaErrorInvalidValue;
+}
 
 // ---------------------------------------------------------------------------------------
 // calculatePairWeight (device.go:135-157) for every pair at once.
