@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -174,10 +175,11 @@ bool build_plan(const tp_policy *p, Prep &out) {
     pl.jt_hi = n - pp;
     pl.n_entries = n - pp - q + 1;
     pl.min_w = min_w;
-    // Slice so that there are >= ~16 items per resident warp (2 x 8 warps x 148 SMs) for the tail,
-    // while one item stays worth >= 4K subsets per lane so that the per-item set-up (unrank, lane
-    // vector: ~500 instructions) stays in the noise.
-    const u64 cap0 = std::min<u64>(std::max<u64>(4096, rq.total / 1200000), 32768);
+    // Slice so that the longest item (one warp, serial) is a few percent of the whole search,
+    // while one item stays worth >= 2K subsets per lane: the per-item set-up (unrank, lane vector)
+    // is latency-bound and measurably costs throughput when items get small (sweep in DESIGN.md).
+    u64 cap0 = std::min<u64>(std::max<u64>(2048, rq.total / 100000), 65536);
+    if (const char *env = getenv("TP_SPLIT_CAP")) cap0 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
     u64 items = 0;
     for (int e = 0; e < pl.n_entries; e++) {
         const int jt = pl.jt_hi - e;

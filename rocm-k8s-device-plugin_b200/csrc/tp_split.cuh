@@ -26,6 +26,10 @@
 #pragma once
 #include "tp_device.cuh"
 
+// Dynamic shared memory of the kernel.  The masked table sits at its very start, so that the
+// unrolled rows address it with immediates.
+extern __shared__ __align__(16) unsigned char tp_split_smem[];
+
 struct TpSplitShared { // block-shared tables (pointers into dynamic shared memory)
     const uint16_t *wp; // [n][rsp] plain weights, reversed positions (all n columns: A sits above M)
     const uint16_t *wm; // [n][M+8] row jx: W for jy < jx, TP_BIG for jy >= jx
@@ -50,37 +54,55 @@ struct TpSplitCfg {
 
 // One row of the triangular nest: all pairs (JX, jy < JX).  Registers past the last valid jy
 // are not touched at all (JX is a compile-time constant), so only an odd JX wastes half a lane-op.
+// The first 16 bytes of the row arrive in `cur`, loaded while the previous row was computing;
+// this row in turn starts the load of row JX-1 into `nxt`, so the shared-memory latency of the
+// short rows (where the leaves spend their time) overlaps the arithmetic.
 template <int M, int JX>
 __device__ __forceinline__ void tp_split_row(const unsigned (&P)[M / 2], const uint4 *__restrict__ wm4,
-                                             unsigned &run) {
+                                             unsigned &run, const uint4 &cur, uint4 &nxt) {
     constexpr int NFULL = JX / 8, REM = JX % 8;
+    if constexpr (JX > 1) nxt = wm4[(JX - 1) * TpSplitCfg<M>::RS4];
     const unsigned px2 = __byte_perm(P[JX / 2], 0, (JX & 1) ? 0x3232 : 0x1010);
     unsigned acc = TP_BIG2 + TP_BIG2;
+    if constexpr (NFULL >= 1) {
+        acc = __viaddmin_u16x2(P[0], cur.x, acc);
+        acc = __viaddmin_u16x2(P[1], cur.y, acc);
+        acc = __viaddmin_u16x2(P[2], cur.z, acc);
+        acc = __viaddmin_u16x2(P[3], cur.w, acc);
 #pragma unroll
-    for (int c = 0; c < NFULL; c++) {
-        const uint4 r = wm4[JX * TpSplitCfg<M>::RS4 + c];
-        acc = __viaddmin_u16x2(P[4 * c + 0], r.x, acc);
-        acc = __viaddmin_u16x2(P[4 * c + 1], r.y, acc);
-        acc = __viaddmin_u16x2(P[4 * c + 2], r.z, acc);
-        acc = __viaddmin_u16x2(P[4 * c + 3], r.w, acc);
-    }
-    if constexpr (REM > 4) {
-        const uint4 r = wm4[JX * TpSplitCfg<M>::RS4 + NFULL];
-        acc = __viaddmin_u16x2(P[4 * NFULL + 0], r.x, acc);
-        acc = __viaddmin_u16x2(P[4 * NFULL + 1], r.y, acc);
-        acc = __viaddmin_u16x2(P[4 * NFULL + 2], r.z, acc);
-        if constexpr (REM > 6) acc = __viaddmin_u16x2(P[4 * NFULL + 3], r.w, acc);
-    } else if constexpr (REM > 0) {
-        const uint2 r = ((const uint2 *)wm4)[(JX * TpSplitCfg<M>::RS4 + NFULL) * 2];
-        acc = __viaddmin_u16x2(P[4 * NFULL + 0], r.x, acc);
-        if constexpr (REM > 2) acc = __viaddmin_u16x2(P[4 * NFULL + 1], r.y, acc);
+        for (int c = 1; c < NFULL; c++) {
+            const uint4 r = wm4[JX * TpSplitCfg<M>::RS4 + c];
+            acc = __viaddmin_u16x2(P[4 * c + 0], r.x, acc);
+            acc = __viaddmin_u16x2(P[4 * c + 1], r.y, acc);
+            acc = __viaddmin_u16x2(P[4 * c + 2], r.z, acc);
+            acc = __viaddmin_u16x2(P[4 * c + 3], r.w, acc);
+        }
+        if constexpr (REM > 4) {
+            const uint4 r = wm4[JX * TpSplitCfg<M>::RS4 + NFULL];
+            acc = __viaddmin_u16x2(P[4 * NFULL + 0], r.x, acc);
+            acc = __viaddmin_u16x2(P[4 * NFULL + 1], r.y, acc);
+            acc = __viaddmin_u16x2(P[4 * NFULL + 2], r.z, acc);
+            if constexpr (REM > 6) acc = __viaddmin_u16x2(P[4 * NFULL + 3], r.w, acc);
+        } else if constexpr (REM > 0) {
+            const uint2 r = ((const uint2 *)wm4)[(JX * TpSplitCfg<M>::RS4 + NFULL) * 2];
+            acc = __viaddmin_u16x2(P[4 * NFULL + 0], r.x, acc);
+            if constexpr (REM > 2) acc = __viaddmin_u16x2(P[4 * NFULL + 1], r.y, acc);
+        }
+    } else { // the whole row sits in the prefetched chunk
+        acc = __viaddmin_u16x2(P[0], cur.x, acc);
+        if constexpr (REM > 2) acc = __viaddmin_u16x2(P[1], cur.y, acc);
+        if constexpr (REM > 4) acc = __viaddmin_u16x2(P[2], cur.z, acc);
+        if constexpr (REM > 6) acc = __viaddmin_u16x2(P[3], cur.w, acc);
     }
     run = __viaddmin_u16x2(acc, px2, run);
 }
 
-#define TP_ROW_CASE(J)                                                        \
-    case J:                                                                   \
-        if constexpr ((J) < M && (J) >= 1) tp_split_row<M, (J)>(P, wm4, run); \
+#define TP_ROW_CASE(J)                                                                  \
+    case J:                                                                             \
+        if constexpr ((J) < M && (J) >= 1) {                                            \
+            if constexpr ((J) & 1) tp_split_row<M, (J)>(P, wm4, run, buf_odd, buf_even); \
+            else tp_split_row<M, (J)>(P, wm4, run, buf_even, buf_odd);                  \
+        }                                                                               \
         [[fallthrough]];
 #define TP_ROW_CASE8(B)                                                                              \
     TP_ROW_CASE(B + 7) TP_ROW_CASE(B + 6) TP_ROW_CASE(B + 5) TP_ROW_CASE(B + 4) TP_ROW_CASE(B + 3) \
@@ -91,6 +113,7 @@ template <int M>
 __device__ __forceinline__ unsigned tp_split_pairs(const unsigned (&P)[M / 2], const uint4 *__restrict__ wm4,
                                                    int start) {
     unsigned run = TP_BIG2 + TP_BIG2;
+    uint4 buf_even = wm4[start * TpSplitCfg<M>::RS4], buf_odd = buf_even; // first chunk of the entry row
     switch (start) {
         TP_ROW_CASE8(120) TP_ROW_CASE8(112) TP_ROW_CASE8(104) TP_ROW_CASE8(96) TP_ROW_CASE8(88) TP_ROW_CASE8(80)
         TP_ROW_CASE8(72) TP_ROW_CASE8(64) TP_ROW_CASE8(56) TP_ROW_CASE8(48) TP_ROW_CASE8(40) TP_ROW_CASE8(32)
@@ -225,7 +248,7 @@ struct TpSplitWalk {
             }
         } else {
             // leaf level: b is the last walked position, the pairs live below it
-            const uint4 *wm4 = (const uint4 *)sh.wm;
+            const uint4 *wm4 = (const uint4 *)tp_split_smem;
             const uint4 *v4 = (const uint4 *)w.va + w.lane;
             const int room = *(volatile int *)s_bound - lb - sb + 1; // > score of (b, pair) <=> no candidate
             for (int b = hi - 1; b >= lo; --b) {
@@ -247,22 +270,22 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
                     const TpReq *__restrict__ rq, const TpPlan *__restrict__ plan, int shard_idx, int shard_cnt,
                     TpScratch sc, unsigned *work_counter) {
     using Cfg = TpSplitCfg<M>;
-    extern __shared__ __align__(16) unsigned char smem[];
+    unsigned char *const smem = tp_split_smem;
     __shared__ int s_bound;
     const int n = rq->n, k = rq->k, p = plan->p, q = plan->q;
     const int n_entries = plan->n_entries;
     const unsigned total_items = plan->total_items;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const TpSmem s = tp_smem_carve(smem, n, k);
+    // layout: masked table first (its row chunks are then compile-time offsets from the start of
+    // shared memory), then the staged request, the plain table, u, and the per-warp areas
+    uint16_t *wm = (uint16_t *)smem;
+    size_t off = (size_t)n * Cfg::RS * 2;
+    const TpSmem s = tp_smem_carve(smem + off, n, k);
     tp_stage_request(s, W, nd, binom_g, rq, k, &s_bound);
-
-    // ---- block-shared 16-bit tables in reversed positions ------------------------------------
-    size_t off = (tp_smem_bytes(n, k) + 15) & ~(size_t)15;
+    off += (tp_smem_bytes(n, k) + 15) & ~(size_t)15;
     const int rsp = tp_split_rsp(n);
     uint16_t *wp = (uint16_t *)(smem + off);
     off += (size_t)n * rsp * 2;
-    uint16_t *wm = (uint16_t *)(smem + off);
-    off += (size_t)n * Cfg::RS * 2;
     uint16_t *t0 = (uint16_t *)(smem + off); // u in reversed positions, all n of them (level 0 of T)
     off += (size_t)TP_MAX_N * 2;
     const size_t per_warp = (size_t)(D + 1) * M * 2 + (size_t)Cfg::NCHUNK * 32 * 16 + 16;
@@ -410,7 +433,7 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
         unsigned P[Cfg::NREG];
         if constexpr (D == 0) {
             tp_split_make_p<M, false>(P, (const uint4 *)va + lane, (const uint4 *)tstack, nullptr, jt);
-            const unsigned run = tp_split_pairs<M>(P, (const uint4 *)wm, jt - 1);
+            const unsigned run = tp_split_pairs<M>(P, (const uint4 *)tp_split_smem, jt - 1);
             const int thr = min(max(*(volatile int *)&s_bound - sA + 1, 0), 0xFFFF);
             const unsigned thr2 = (unsigned)thr * 0x10001u;
             if (__vminu2(run, thr2) != thr2 && active)
