@@ -72,8 +72,9 @@ typedef struct tp_topology {
     const uint8_t *weight;
 } tp_topology;
 
+#define TP_DEVICE_NONE (-2) /* tp_options.cuda_device: host-only handle (validation, tp_decode); searches fail */
 typedef struct tp_options {
-    int32_t cuda_device;        /* ordinal; -1 = the current device */
+    int32_t cuda_device;        /* ordinal; -1 = the current device; TP_DEVICE_NONE = no device */
     int32_t kernel;             /* 0 = auto; else force a kernel variant (tests / profiling) */
     uint64_t exhaustive_limit;  /* 0 = default; above this many subsets only Family members are enumerated */
     int32_t max_inflight;       /* 0 = default (8): concurrent tp_allocate calls before callers queue */

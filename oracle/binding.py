@@ -31,7 +31,8 @@ class _Result(C.Structure):
 class _ExhResult(C.Structure):
     _fields_ = [("score", C.c_int), ("m", C.c_int), ("scored", C.c_ulonglong),
                 ("total", C.c_ulonglong), ("slow", C.c_ulonglong), ("n_free", C.c_int),
-                ("k_free", C.c_int), ("n_groups", C.c_int), ("threads", C.c_int)]
+                ("k_free", C.c_int), ("n_groups", C.c_int), ("threads", C.c_int),
+                ("key_hi", C.c_ulonglong), ("key_lo", C.c_ulonglong)]
 
 
 @dataclass

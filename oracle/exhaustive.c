@@ -47,6 +47,12 @@ typedef struct ref_exh_result {
     unsigned long long slow;     /* Family/RefKey evaluations */
     int n_free, k_free, n_groups;
     int threads;
+    /* The winner in the product's wire format (tp_key, include/tp_allocator.h), restated here
+     * from that header's description: hi = score:16 | groups:8 | first 40 bits of the group
+     * sequence, lo = the remaining 64 bits; digits are ceil(log2(groups)) bits, first digit
+     * most significant, in a 104-bit field.  Lets CPU-only tests exercise the multi-rank
+     * min-reduce + tp_decode path with keys produced by the oracle. */
+    unsigned long long key_hi, key_lo;
 } ref_exh_result;
 
 typedef struct exh_key {
@@ -331,6 +337,14 @@ int ref_exhaustive_allocate(const ref_policy *p, const char *const *avail, int n
     if (res) {
         res->score = best.score;
         res->m = best.m;
+        int dbits = 1;
+        while ((1 << dbits) < x->n_groups) dbits++;
+        unsigned __int128 field = 0;
+        for (int i = 0; i < best.m; i++)
+            field |= (unsigned __int128)(unsigned)best.sigma[i] << (104 - (i + 1) * dbits);
+        res->key_hi = ((unsigned long long)best.score << 48) | ((unsigned long long)best.m << 40) |
+                      (unsigned long long)(field >> 64);
+        res->key_lo = (unsigned long long)field;
     }
     /* Output order of besteffort_policy.go:141-148: candidate order = group
      * sequence, ascending NodeId inside a group, required last in request order. */

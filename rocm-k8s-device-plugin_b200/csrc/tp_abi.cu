@@ -54,6 +54,7 @@ struct tp_policy {
     std::vector<int32_t> node_id, group, parent_rank;
     std::vector<uint8_t> weight;
     bool weights_empty = true; // len(p2pWeights) == 0
+    bool host_only = false;    // created with TP_DEVICE_NONE: no CUDA state at all
     int cuda_device = 0, sm_count = 148;
     int kernel = 0;
     u64 exhaustive_limit = 0;
@@ -493,6 +494,12 @@ int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
     p->kernel = o ? o->kernel : 0;
     p->exhaustive_limit = o ? o->exhaustive_limit : 0;
     int dev = o ? o->cuda_device : -1;
+    if (dev == TP_DEVICE_NONE) { // host-only handle: validation, sharding arithmetic and tp_decode work,
+        p->host_only = true;     // every entry point that would search returns TP_ERR_CUDA
+        p->cuda_device = -1;
+        *out = p;
+        return TP_OK;
+    }
     if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) { delete p; return TP_ERR_CUDA; }
     p->cuda_device = dev;
     int rc = [&]() -> int {
@@ -523,6 +530,10 @@ int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
 
 void tp_destroy(tp_policy *p) {
     if (!p) return;
+    if (p->host_only) {
+        delete p;
+        return;
+    }
     {
         DeviceGuard guard(p->cuda_device);
         for (Ctx &c : p->ctxs) free_ctx(c);
@@ -541,6 +552,7 @@ int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32
     if (pr.status) return pr.status;
     if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; } // :110-112, as given
     if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }   // :114-116
+    if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
     DeviceGuard guard(p->cuda_device);
     CtxLease lease(p);
     TpKey key;
@@ -570,6 +582,7 @@ int tp_search_resident(tp_policy *p, const int32_t *avail, int32_t n_avail, cons
     prepare(p, avail, n_avail, req, n_req, size, pr);
     if (pr.status) return pr.status;
     if (pr.shortcut) return 1;
+    if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
     DeviceGuard guard(p->cuda_device);
     CtxLease lease(p);
     Ctx &c = lease.ctx();
@@ -592,6 +605,7 @@ int tp_search_shard(tp_policy *p, const int32_t *avail, int32_t n_avail, const i
     prepare(p, avail, n_avail, req, n_req, size, pr);
     if (pr.status) return pr.status;
     if (pr.shortcut) return 1;
+    if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
     DeviceGuard guard(p->cuda_device);
     CtxLease lease(p);
     TpKey k;
@@ -628,7 +642,8 @@ int tp_prepare(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_
     tp_prepared *q = new (std::nothrow) tp_prepared();
     if (!q) return TP_ERR_BAD_ARGUMENT;
     prepare(p, avail, n_avail, req, n_req, size, q->pr);
-    int rc = q->pr.status ? q->pr.status : q->pr.shortcut ? 1 : q->pr.family_only ? TP_ERR_TOO_LARGE : 0;
+    int rc = q->pr.status ? q->pr.status : q->pr.shortcut ? 1 : q->pr.family_only ? TP_ERR_TOO_LARGE
+             : p->host_only ? TP_ERR_CUDA : 0;
     if (rc) {
         delete q;
         return rc;
