@@ -228,7 +228,7 @@ def main():
         dist.all_reduce(scored)
     total_subsets = int(scored.item())
     got = pol.Decode(ids, req, size, (key_hi, 0))
-    assert got == expected and (key_hi >> 48) == score, (got, key_hi)
+    assert got == expected and (key_hi >> 40) == score, (got, key_hi)
     assert total_subsets == 28987537150, total_subsets
     value = total_subsets * args.steps / (dev_ms * 1e-3)
 

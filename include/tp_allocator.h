@@ -85,8 +85,8 @@ typedef struct tp_options {
  * order is the order in which the reference's BFS emits candidates
  * (device.go:375-440) under the strict `<` of besteffort_policy.go:133-140. */
 typedef struct tp_key {
-    uint64_t hi; /* score:16 | groups:8 | first 40 bits of the group sequence */
-    uint64_t lo; /* rest of the group sequence; 0 whenever (size-len(required))*ceil(log2 groups) <= 40 */
+    uint64_t hi; /* 0:1 | score:23 | groups:8 | first 32 bits of the group sequence */
+    uint64_t lo; /* rest of the group sequence; 0 whenever (size-len(required))*ceil(log2 groups) <= 32 */
 } tp_key;
 
 typedef struct tp_result {

@@ -48,9 +48,9 @@ typedef struct ref_exh_result {
     int n_free, k_free, n_groups;
     int threads;
     /* The winner in the product's wire format (tp_key, include/tp_allocator.h), restated here
-     * from that header's description: hi = score:16 | groups:8 | first 40 bits of the group
+     * from that header's description: hi = 0:1 | score:23 | groups:8 | first 32 bits of the group
      * sequence, lo = the remaining 64 bits; digits are ceil(log2(groups)) bits, first digit
-     * most significant, in a 104-bit field.  Lets CPU-only tests exercise the multi-rank
+     * most significant, in a 96-bit field.  Lets CPU-only tests exercise the multi-rank
      * min-reduce + tp_decode path with keys produced by the oracle. */
     unsigned long long key_hi, key_lo;
 } ref_exh_result;
@@ -341,8 +341,8 @@ int ref_exhaustive_allocate(const ref_policy *p, const char *const *avail, int n
         while ((1 << dbits) < x->n_groups) dbits++;
         unsigned __int128 field = 0;
         for (int i = 0; i < best.m; i++)
-            field |= (unsigned __int128)(unsigned)best.sigma[i] << (104 - (i + 1) * dbits);
-        res->key_hi = ((unsigned long long)best.score << 48) | ((unsigned long long)best.m << 40) |
+            field |= (unsigned __int128)(unsigned)best.sigma[i] << (96 - (i + 1) * dbits);
+        res->key_hi = ((unsigned long long)best.score << 40) | ((unsigned long long)best.m << 32) |
                       (unsigned long long)(field >> 64);
         res->key_lo = (unsigned long long)field;
     }

@@ -44,7 +44,8 @@ struct Prep {
     int shortcut = 0;    // 1: return available as given; 2: return required as given
     int n_req = 0;
     int kernel = TP_KERNEL_LEX;
-    bool family_only = false;
+    bool family_only = false; // not enumerable and not within the FAMILY kernel's limits either
+    u64 family_masks = 0;     // kernel FAMILY: 2^groups bitmasks to visit
 };
 
 } // namespace
@@ -302,6 +303,14 @@ void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_
     const u64 limit = p->exhaustive_limit ? p->exhaustive_limit : (1ull << 38);
     if (rq.k > TP_MAX_K || rq.total > limit || rq.k * dbits > TP_SIGMA_BITS) out.family_only = true;
     out.kernel = TP_KERNEL_LEX;
+    // Family-only search: when the space cannot be enumerated (or when forced, for cross-checks).
+    const bool family_fits = rq.n_groups <= TP_FAMILY_MAX_GROUPS && std::min(rq.n_groups, rq.k) * dbits <= TP_SIGMA_BITS;
+    if ((out.family_only || p->kernel == TP_KERNEL_FAMILY) && family_fits) {
+        out.kernel = TP_KERNEL_FAMILY;
+        out.family_only = false;
+        out.family_masks = 1ull << rq.n_groups;
+        return;
+    }
     if (!out.family_only && p->kernel != TP_KERNEL_LEX && build_plan(p, out)) out.kernel = TP_KERNEL_SPLIT;
 }
 
@@ -344,12 +353,13 @@ cudaError_t upload_request(Ctx &c, const Prep &pr) {
 bool shard_nonempty(const Prep &pr, int idx, int cnt) {
     if (pr.kernel == TP_KERNEL_SPLIT) return (u64)idx < pr.plan.total_items;
     u64 lo, hi;
-    shard_range(pr.rq.total, idx, cnt, lo, hi);
+    shard_range(pr.kernel == TP_KERNEL_FAMILY ? pr.family_masks : pr.rq.total, idx, cnt, lo, hi);
     return hi > lo;
 }
 
 // Subsets shard (idx of cnt) scores in one launch.
 u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
+    if (pr.kernel == TP_KERNEL_FAMILY) return 0; // Family members are counted by the kernel only
     if (pr.kernel != TP_KERNEL_SPLIT) {
         u64 lo, hi;
         shard_range(pr.rq.total, idx, cnt, lo, hi);
@@ -382,6 +392,10 @@ cudaError_t launch_search(tp_policy *p, Ctx &c, const Prep &pr, int idx, int cnt
         return tp_launch_exhaustive_split(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, c.d_plan, pr.plan, idx, cnt,
                                           sc, c.d_counter, p->sm_count, st, li);
     u64 lo, hi;
+    if (pr.kernel == TP_KERNEL_FAMILY) {
+        shard_range(pr.family_masks, idx, cnt, lo, hi);
+        return tp_launch_family(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, lo, hi, sc, p->sm_count, st, li);
+    }
     shard_range(pr.rq.total, idx, cnt, lo, hi);
     return tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, lo, hi, sc, p->sm_count, st, li);
 }

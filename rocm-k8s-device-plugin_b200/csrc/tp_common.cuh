@@ -19,7 +19,9 @@
 
 #define TP_MAX_N TP_MAX_DEVICES
 #define TP_MAX_K TP_MAX_SUBSET
-#define TP_SIGMA_BITS 104 /* bits of the packed group sequence: 40 in key.hi + 64 in key.lo */
+#define TP_SIGMA_BITS 96 /* bits of the packed group sequence: 32 in key.hi + 64 in key.lo */
+#define TP_KEY_SCORE_SHIFT 40
+#define TP_KEY_GROUPS_SHIFT 32
 
 // One prepared request, as the kernels read it (device resident, ~1 KB).
 struct TpReq {
@@ -50,13 +52,14 @@ __host__ __device__ __forceinline__ bool tp_key_less(const TpKey &a, const TpKey
     return a.hi < b.hi || (a.hi == b.hi && a.lo < b.lo);
 }
 
-// score:16 | m:8 | sigma digits, most significant first, dbits each, in a 104-bit field.
+// 0:1 | score:23 | m:8 | sigma digits, most significant first, dbits each, in a 96-bit field.
 __host__ __device__ __forceinline__ void tp_key_begin(TpKey &k, int score, int m) {
-    k.hi = ((unsigned long long)(unsigned)score << 48) | ((unsigned long long)(unsigned)m << 40);
+    k.hi = ((unsigned long long)(unsigned)score << TP_KEY_SCORE_SHIFT) |
+           ((unsigned long long)(unsigned)m << TP_KEY_GROUPS_SHIFT);
     k.lo = 0;
 }
 __host__ __device__ __forceinline__ void tp_key_put(TpKey &k, int i, int dbits, unsigned digit) {
-    int shift = TP_SIGMA_BITS - (i + 1) * dbits; // bit position inside the 104-bit field
+    int shift = TP_SIGMA_BITS - (i + 1) * dbits; // bit position inside the 96-bit field
     if (shift >= 64) {
         k.hi |= (unsigned long long)digit << (shift - 64);
     } else if (shift + dbits <= 64) {
@@ -77,8 +80,8 @@ __host__ __device__ __forceinline__ unsigned tp_key_get(const TpKey &k, int i, i
         v = (k.lo >> shift) | (k.hi << (64 - shift));
     return (unsigned)(v & ((1ull << dbits) - 1));
 }
-__host__ __device__ __forceinline__ int tp_key_score(const TpKey &k) { return (int)(k.hi >> 48); }
-__host__ __device__ __forceinline__ int tp_key_groups(const TpKey &k) { return (int)((k.hi >> 40) & 0xFF); }
+__host__ __device__ __forceinline__ int tp_key_score(const TpKey &k) { return (int)(k.hi >> TP_KEY_SCORE_SHIFT); }
+__host__ __device__ __forceinline__ int tp_key_groups(const TpKey &k) { return (int)((k.hi >> TP_KEY_GROUPS_SHIFT) & 0xFF); }
 
 // Per-launch scratch in global memory: one partial winner per block, reduced by the
 // last block to finish (ticket), so one launch yields the final key with no second kernel.

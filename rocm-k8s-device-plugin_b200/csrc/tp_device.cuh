@@ -37,7 +37,7 @@ static __device__ __noinline__ bool tp_family_key(u64 p0, u64 p1, int k, int sco
         i = j;
     }
     if (partial >= 0) tp_key_put(key, n_whole, dbits, (unsigned)partial);
-    key.hi |= (u64)m << 40;
+    key.hi |= (u64)m << TP_KEY_GROUPS_SHIFT;
     out = key;
     return true;
 }

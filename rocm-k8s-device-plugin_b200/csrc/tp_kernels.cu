@@ -151,6 +151,124 @@ cudaError_t tp_launch_exhaustive_lex(const uint8_t *d_weight, int n_devices, con
     return cudaErrorInvalidValue;
 }
 
+// ---------------------------------------------------------------------------------------
+// Kernel FAMILY: requests whose C(n,k') cannot be enumerated (the reference's own test asks
+// for 30 of 63, 8.6e17 subsets, besteffort_policy_test.go:131-134).  Only Family members can
+// win, and a Family member is (set T of whole groups, optional partial group p): one thread
+// per bitmask T over the <= 24 groups with free devices, scoring from group-level sums that
+// the block builds once in shared memory.  This is the set the reference's BFS emits
+// (device.go:375-440), each member once instead of once per ordering of T.
+// ---------------------------------------------------------------------------------------
+#define TP_FAMILY_THREADS 256
+
+__global__ void __launch_bounds__(TP_FAMILY_THREADS)
+tp_family(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g, const TpReq *__restrict__ rq,
+          u64 mask_lo, u64 mask_hi, TpScratch sc) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    __shared__ int s_bound;
+    const int n = rq->n, k = rq->k, G = rq->n_groups, dbits = rq->dbits;
+    const TpSmem s = tp_smem_carve(smem, n, 1);
+    tp_stage_request(s, W, nd, binom_g, rq, 1, &s_bound); // binomials are not used here (K = 1 keeps them tiny)
+    size_t off = (tp_smem_bytes(n, 1) + 15) & ~(size_t)15;
+    unsigned *gW = (unsigned *)(smem + off);       // [G][G] weight between two whole groups
+    off += (size_t)G * G * 4;
+    unsigned *gI = (unsigned *)(smem + off);       // [G]    pairs inside a whole group + its unary terms
+    off += (size_t)G * 4;
+    unsigned *pI = (unsigned *)(smem + off);       // [n]    same for the prefix of the group ending at position i
+    off += (size_t)n * 4;
+    unsigned *pX = (unsigned *)(smem + off);       // [n][G] prefix ending at i  x  whole group g
+    for (int i = threadIdx.x; i < n * G; i += blockDim.x) {
+        const int e = i / G, g = i - e * G;
+        unsigned acc = 0;
+        if (g != s.group[e])
+            for (int t = s.gstart[s.group[e]]; t <= e; t++)
+                for (int j = 0; j < s.gsize[g]; j++) acc += s.w[t * s.stride + s.gstart[g] + j];
+        pX[i] = acc;
+    }
+    for (int e = threadIdx.x; e < n; e += blockDim.x) {
+        unsigned acc = 0;
+        for (int t = s.gstart[s.group[e]]; t <= e; t++) {
+            acc += s.u[t];
+            for (int t2 = s.gstart[s.group[e]]; t2 < t; t2++) acc += s.w[t2 * s.stride + t];
+        }
+        pI[e] = acc;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < G * G; i += blockDim.x) {
+        const int g = i / G, h = i - g * G;
+        gW[i] = (g == h) ? 0u : pX[(s.gstart[g] + s.gsize[g] - 1) * G + h];
+    }
+    for (int g = threadIdx.x; g < G; g += blockDim.x) gI[g] = pI[s.gstart[g] + s.gsize[g] - 1];
+    if (threadIdx.x == 0) s_bound = 0x7FFFFFFF; // the exhaustive kernels' seed is meaningless at K = 1
+    __syncthreads();
+
+    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+    u64 counted = 0;
+    int bound = 0x7FFFFFFF;
+    for (u64 T = mask_lo + (u64)blockIdx.x * blockDim.x + threadIdx.x; T < mask_hi; T += (u64)gridDim.x * blockDim.x) {
+        int sum = 0, m0 = 0;
+        unsigned base = (unsigned)rq->c_req;
+        for (int g = 0; g < G; g++)
+            if ((T >> g) & 1) {
+                sum += s.gsize[g];
+                m0++;
+                base += gI[g];
+                for (int h = 0; h < g; h++)
+                    if ((T >> h) & 1) base += gW[g * G + h];
+            }
+        if (sum > k) continue;
+        auto emit = [&](unsigned score, int partial) {
+            counted++;
+            if ((int)score > bound) return;
+            TpKey key;
+            tp_key_begin(key, (int)score, m0 + (partial >= 0 ? 1 : 0));
+            int d = 0;
+            for (int g = 0; g < G; g++)
+                if ((T >> g) & 1) tp_key_put(key, d++, dbits, (unsigned)g);
+            if (partial >= 0) tp_key_put(key, d, dbits, (unsigned)partial);
+            if (tp_key_less(key, best)) best = key;
+            bound = (int)score;
+        };
+        if (sum == k) {
+            if (m0 > 0) emit(base, -1);
+            continue;
+        }
+        const int c = k - sum; // devices still to take from one partial group
+        for (int p = 0; p < G; p++) {
+            if (((T >> p) & 1) || s.gsize[p] <= c) continue;
+            const int last = s.gstart[p] + c - 1;
+            unsigned score = base + pI[last];
+            for (int g = 0; g < G; g++)
+                if ((T >> g) & 1) score += pX[last * G + g];
+            emit(score, p);
+        }
+    }
+    tp_block_finish(best, counted, sc);
+}
+
+cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const u64 *d_binom, const TpReq *d_rq,
+                             const TpReq &h, u64 mask_lo, u64 mask_hi, const TpScratch &sc, int sm_count,
+                             cudaStream_t st, TpLaunchInfo *info) {
+    const int G = h.n_groups;
+    const size_t smem = ((tp_smem_bytes(h.n, 1) + 15) & ~(size_t)15) + (size_t)G * G * 4 + (size_t)G * 4 +
+                        (size_t)h.n * 4 + (size_t)h.n * G * 4;
+    cudaError_t e = cudaFuncSetAttribute(tp_family, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const u64 span = mask_hi - mask_lo;
+    u64 blocks = (span + TP_FAMILY_THREADS - 1) / TP_FAMILY_THREADS;
+    const u64 cap = (u64)sm_count * 8 < TP_MAX_BLOCKS ? (u64)sm_count * 8 : TP_MAX_BLOCKS;
+    if (blocks > cap) blocks = cap;
+    if (blocks == 0) blocks = 1;
+    tp_family<<<(unsigned)blocks, TP_FAMILY_THREADS, smem, st>>>(d_weight, n_devices, d_binom, d_rq, mask_lo,
+                                                                 mask_hi, sc);
+    if (info) {
+        info->launches = 1;
+        info->blocks = (int)blocks;
+        info->threads = TP_FAMILY_THREADS;
+    }
+    return cudaGetLastError();
+}
+
 // Kernel SPLIT: pick the narrowest lane vector that holds every pivot (n - p positions).
 cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, const u64 *d_binom,
                                        const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, const TpPlan &hp,

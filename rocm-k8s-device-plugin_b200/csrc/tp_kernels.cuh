@@ -39,6 +39,13 @@ cudaError_t tp_launch_exhaustive_lex(const uint8_t *d_weight, int n_devices, con
                                      unsigned long long hi, const TpScratch &scratch, int sm_count,
                                      cudaStream_t stream, TpLaunchInfo *info);
 
+// Family members only: one thread per bitmask over the groups with free devices, masks [lo, hi).
+#define TP_FAMILY_MAX_GROUPS 24
+cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                             const TpReq *d_rq, const TpReq &h_rq, unsigned long long mask_lo,
+                             unsigned long long mask_hi, const TpScratch &scratch, int sm_count,
+                             cudaStream_t stream, TpLaunchInfo *info);
+
 cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t *d_numa, const int32_t *d_link,
                                     uint8_t *d_out, cudaStream_t stream);
 

@@ -57,8 +57,6 @@ def test_reference_cases(pols, name):
     """besteffort_policy_test.go:53-160 replayed on the GPU policy."""
     ref, pol = pols(name)
     for case in topo.golden("reference_cases.json")[name]:
-        if case["size"] > 12:
-            continue  # k=30 of 63: covered by the Family kernel tests
         out = pol.Allocate(case["available"], case.get("required") or [], case["size"])
         assert len(out) == case["size"]
         if case.get("expected") is not None:
@@ -166,3 +164,40 @@ def test_split_kernel_all_depths(pols, name, sizes):
             assert lex.last["key"] == pol.last["key"]
     assert tp.KERNEL_SPLIT in seen
     lex.close()
+
+
+@pytest.mark.parametrize("name", ["mi308", "cpx", "c4", "missing", "hives"])
+def test_family_kernel(pols, name):
+    """Kernel FAMILY: (a) forced on enumerable requests it must equal the exhaustive kernels' key;
+    (b) on requests far beyond enumeration (the reference's own 30-of-63 case and larger) it must
+    equal the reference's BFS."""
+    ref, pol = pols(name)
+    devs = ref.devices
+    fam = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_FAMILY)
+    fam.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs],
+                        topo.fixture_topology(name)[1] if name in FIXTURES else SYNTH[name]()[1])
+    ids = [d.Id for d in devs]
+    gen = topo.SplitMix64(0xFA111 + len(ids))
+    for _ in range(60):  # (a)
+        av, rq, k = topo.random_request(gen, ids, kmax=6)
+        want = ref.Allocate(av, rq, k)
+        if not ref.last["searched"]:
+            continue
+        assert fam.Allocate(av, rq, k) == want and fam.last["kernel"] == tp.KERNEL_FAMILY
+        assert pol.Allocate(av, rq, k) == want and pol.last["key"] == fam.last["key"]
+    big = 0
+    for _ in range(40):  # (b)
+        av = [i for i in ids if gen.chance(0.85)]
+        k = 17 + gen.below(max(min(len(av) - 18, 24), 1))
+        if len(av) <= k:
+            continue
+        rq = av[:gen.below(3)]
+        want = ref.Allocate(av, rq, k)
+        got = pol.Allocate(av, rq, k)
+        assert got == want, (name, len(av), k)
+        assert pol.last["score"] == ref.last["score"] and pol.last["subsets_scored"] > 0
+        if k - len(rq) > tp.TP_MAX_SUBSET:
+            assert pol.last["kernel"] == tp.KERNEL_FAMILY
+            big += 1
+    assert big > 10
+    fam.close()
