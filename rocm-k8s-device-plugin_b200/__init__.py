@@ -331,3 +331,40 @@ def measure_int_peak(cuda_device=0, variant=0) -> float:
     if rc < 0:
         raise AllocatorError(rc, strerror(rc))
     return g.value
+
+
+def allocate_batch(pol: BestEffortPolicy, requests):
+    """tp_allocate_batch: requests = [(available ids, required ids, size)], the ContainerRequests of
+    one GetPreferredAllocation RPC (amdgpu.go:307-317).  Returns ([ids] or AllocatorError per request, infos)."""
+    n = len(requests)
+    arr = (TpRequest * max(n, 1))()
+    keep = []
+    stride = max([r[2] for r in requests] + [1])
+    for i, (av, rq, size) in enumerate(requests):
+        a, r = _i32(pol.indices(av)), _i32(pol.indices(rq or []))
+        keep.append((a, r))
+        arr[i] = TpRequest(a, len(av), r, len(rq or []), size)
+    out = (C.c_int32 * (max(n, 1) * stride))()
+    status = (C.c_int32 * max(n, 1))()
+    infos = (TpResult * max(n, 1))()
+    rc = lib().tp_allocate_batch(pol.handle, n, arr, out, stride, status, infos)
+    if rc < 0:
+        raise AllocatorError(rc, strerror(rc))
+    res = []
+    for i in range(n):
+        if status[i] < 0:
+            res.append(AllocatorError(status[i], strerror(status[i])))
+        else:
+            res.append([pol.devices[j].Id for j in out[i * stride:i * stride + status[i]]])
+    return res, [infos[i].dict() for i in range(n)]
+
+
+def build_weights(group, numa_node, link_type, cuda_device=0):
+    """tp_build_weights: calculatePairWeight (device.go:135-157) for all pairs on the GPU.
+    link_type is an n*n row-major list of KFD link types, -1 where no link entry exists."""
+    n = len(group)
+    out = (C.c_uint8 * (n * n))()
+    rc = lib().tp_build_weights(n, _i32(group), _i32(numa_node), _i32(link_type), out, cuda_device)
+    if rc < 0:
+        raise AllocatorError(rc, strerror(rc))
+    return list(out)
