@@ -6,6 +6,7 @@
 // (device.go:310-351), and the NodeId -> output order mapping (:141-148).  The search
 // itself (device.go:353-442 + the argmin) always runs on the GPU; there is no CPU path.
 #include <algorithm>
+#include <atomic>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -34,6 +35,15 @@ struct Ctx { // one in-flight call: stream, events, pinned staging, device reque
     unsigned char *d_scratch = nullptr;
     TpScratch scratch{};
     unsigned *d_counter = nullptr; // work counter of kernel SPLIT (a word of d_scratch)
+    // latency path: the kernel writes key, count and a flag straight into this mapped host buffer
+    struct Fast {
+        TpKey key;
+        u64 scored;
+        volatile unsigned flag;
+        unsigned pad;
+    } *h_fast = nullptr;
+    void *d_fast = nullptr;
+    unsigned epoch = 0;
 };
 
 // Everything the host derives from one request before (and after) the GPU search.
@@ -121,6 +131,9 @@ int init_ctx(tp_policy *p, Ctx &c) {
     TP_CUDA(p, cudaHostAlloc((void **)&c.h_req, sizeof(TpReq) + sizeof(TpPlan), cudaHostAllocDefault));
     TP_CUDA(p, cudaHostAlloc((void **)&c.h_out, sizeof(Ctx::Out), cudaHostAllocDefault));
     TP_CUDA(p, cudaMalloc((void **)&c.d_req, sizeof(TpReq) + sizeof(TpPlan)));
+    TP_CUDA(p, cudaHostAlloc((void **)&c.h_fast, sizeof(Ctx::Fast), cudaHostAllocMapped));
+    memset((void *)c.h_fast, 0, sizeof(Ctx::Fast));
+    TP_CUDA(p, cudaHostGetDevicePointer(&c.d_fast, (void *)c.h_fast, 0));
     c.h_plan = (TpPlan *)((unsigned char *)c.h_req + sizeof(TpReq));
     c.d_plan = (TpPlan *)((unsigned char *)c.d_req + sizeof(TpReq));
     const size_t partial_bytes = sizeof(TpKey) * TP_MAX_BLOCKS;
@@ -143,6 +156,7 @@ void free_ctx(Ctx &c) {
     if (c.ev1) cudaEventDestroy(c.ev1);
     if (c.h_req) cudaFreeHost(c.h_req);
     if (c.h_out) cudaFreeHost(c.h_out);
+    if (c.h_fast) cudaFreeHost((void *)c.h_fast);
     if (c.d_req) cudaFree(c.d_req);
     if (c.d_scratch) cudaFree(c.d_scratch);
 }
@@ -311,6 +325,7 @@ void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_
         out.family_masks = 1ull << rq.n_groups;
         return;
     }
+    if (p->kernel == TP_KERNEL_AUTO && rq.total <= TP_FAST_MAX_SUBSETS) return; // small: LEX (latency path), no plan
     if (!out.family_only && p->kernel != TP_KERNEL_LEX && build_plan(p, out)) out.kernel = TP_KERNEL_SPLIT;
 }
 
@@ -398,6 +413,43 @@ cudaError_t launch_search(tp_policy *p, Ctx &c, const Prep &pr, int idx, int cnt
     }
     shard_range(pr.rq.total, idx, cnt, lo, hi);
     return tp_launch_exhaustive_lex(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, lo, hi, sc, p->sm_count, st, li);
+}
+
+// Latency path for small searches (BASELINE configs C1/C2): one single-block launch with the
+// descriptor as a kernel parameter; the result lands in mapped host memory and is picked up by
+// polling its flag, so the call makes no memcpy, records no event and never blocks in the driver.
+int run_search_fast(tp_policy *p, Ctx &c, const Prep &pr, TpKey *key, tp_result *info) {
+    const unsigned epoch = ++c.epoch ? c.epoch : ++c.epoch; // never 0
+    TP_CUDA(p, tp_launch_exhaustive_lex_small(p->d_weight, p->n, p->d_binom, pr.rq, c.d_fast, epoch, c.stream));
+    unsigned spins = 0;
+    while (c.h_fast->flag != epoch) {
+        if ((++spins & 0xFFFF) == 0) { // a failed launch would never raise the flag
+            cudaError_t e = cudaStreamQuery(c.stream);
+            if (e != cudaSuccess && e != cudaErrorNotReady) TP_CUDA(p, e);
+            if (e == cudaSuccess && c.h_fast->flag != epoch) TP_CUDA(p, cudaStreamSynchronize(c.stream));
+        }
+#if defined(__x86_64__)
+        __builtin_ia32_pause();
+#endif
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    key->hi = c.h_fast->key.hi;
+    key->lo = c.h_fast->key.lo;
+    if (info) {
+        info->searched = 1;
+        info->kernel = TP_KERNEL_LEX;
+        info->subsets_scored = c.h_fast->scored;
+        info->subsets_total = pr.rq.total;
+        info->kernel_ms = 0.f; // not timed on this path (no events)
+        info->gpu_launches = 1;
+        info->key.hi = key->hi;
+        info->key.lo = key->lo;
+        if (key->hi != TP_KEY_INF_HI) {
+            info->score = tp_key_score(*key);
+            info->groups_touched = tp_key_groups(*key);
+        }
+    }
+    return 0;
 }
 
 // Upload the prepared request, run the search over shard (idx of cnt) `iters` times, fetch the key.
@@ -570,7 +622,10 @@ int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32
     DeviceGuard guard(p->cuda_device);
     CtxLease lease(p);
     TpKey key;
-    int rc = run_search(p, lease.ctx(), pr, 0, 1, 1, true, &key, info, nullptr);
+    const bool fast = pr.kernel != TP_KERNEL_FAMILY && !pr.family_only && pr.rq.total <= TP_FAST_MAX_SUBSETS &&
+                      p->kernel == TP_KERNEL_AUTO;
+    int rc = fast ? run_search_fast(p, lease.ctx(), pr, &key, info)
+                  : run_search(p, lease.ctx(), pr, 0, 1, 1, true, &key, info, nullptr);
     if (rc) return rc;
     return decode(pr, key, req, out);
 }

@@ -19,18 +19,15 @@
 #define TP_LEX_THREADS 256
 
 template <int K>
-__global__ void __launch_bounds__(TP_LEX_THREADS)
-tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
-                  const TpReq *__restrict__ rq, u64 lo, u64 hi, u64 per_thread, TpScratch sc) {
+__device__ __forceinline__ void tp_lex_body(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
+                                            const TpReq *__restrict__ rq, u64 lo, u64 hi, u64 per_thread,
+                                            TpKey &best, u64 &counted) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_bound;
     const int n = rq->n;
     const TpSmem s = tp_smem_carve(smem, n, K);
     tp_stage_request(s, W, nd, binom_g, rq, K, &s_bound);
     const int stride = s.stride, dbits = rq->dbits;
-
-    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
-    u64 counted = 0;
     const u64 gtid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     u64 my_lo = lo + gtid * per_thread;
     if (my_lo < hi) {
@@ -107,7 +104,91 @@ tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
             level = j;
         }
     }
+}
+
+template <int K>
+__global__ void __launch_bounds__(TP_LEX_THREADS)
+tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
+                  const TpReq *__restrict__ rq, u64 lo, u64 hi, u64 per_thread, TpScratch sc) {
+    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+    u64 counted = 0;
+    tp_lex_body<K>(W, nd, binom_g, rq, lo, hi, per_thread, best, counted);
     tp_block_finish(best, counted, sc);
+}
+
+// Latency path (the 28- and 70-subset requests of BASELINE configs C1/C2): one block, the
+// request descriptor travels as a kernel parameter (no H2D copy), and the winner is written
+// straight into mapped host memory followed by a flag the caller polls (no D2H copy, no
+// stream synchronisation).  Same body as tp_exhaustive_lex.
+struct TpFastOut {
+    TpKey key;
+    u64 scored;
+    unsigned flag;
+    unsigned pad;
+};
+
+template <int K>
+__global__ void __launch_bounds__(TP_LEX_THREADS)
+tp_exhaustive_lex_small(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
+                        const __grid_constant__ TpReq rq, u64 lo, u64 hi, u64 per_thread,
+                        TpFastOut *__restrict__ out, unsigned epoch) {
+    __shared__ TpKey s_red[32];
+    __shared__ u64 s_cnt[32];
+    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+    u64 counted = 0;
+    tp_lex_body<K>(W, nd, binom_g, &rq, lo, hi, per_thread, best, counted);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    best = tp_warp_min_key(best);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) counted += __shfl_xor_sync(0xFFFFFFFFu, counted, off);
+    if (lane == 0) {
+        s_red[warp] = best;
+        s_cnt[warp] = counted;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+        u64 c = 0;
+        if (lane < nwarps) {
+            k = s_red[lane];
+            c = s_cnt[lane];
+        }
+        k = tp_warp_min_key(k);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
+        if (lane == 0) {
+            out->key = k;
+            out->scored = c;
+            __threadfence_system();
+            *(volatile unsigned *)&out->flag = epoch;
+        }
+    }
+}
+
+template <int K>
+static cudaError_t launch_lex_small_k(const uint8_t *W, int nd, const u64 *binom, const TpReq &h, void *d_out,
+                                      unsigned epoch, cudaStream_t st) {
+    const u64 span = h.total;
+    u64 per_thread = (span + TP_LEX_THREADS - 1) / TP_LEX_THREADS;
+    if (per_thread == 0) per_thread = 1;
+    const u64 threads = (span + per_thread - 1) / per_thread;
+    int block = (int)((threads + 31) / 32 * 32);
+    if (block == 0) block = 32;
+    tp_exhaustive_lex_small<K><<<1, block, tp_smem_bytes(h.n, K), st>>>(W, nd, binom, h, 0, span, per_thread,
+                                                                        (TpFastOut *)d_out, epoch);
+    return cudaGetLastError();
+}
+
+cudaError_t tp_launch_exhaustive_lex_small(const uint8_t *d_weight, int n_devices, const u64 *d_binom,
+                                           const TpReq &h, void *d_out_mapped, unsigned epoch, cudaStream_t st) {
+#define TP_CASE(KK) \
+    case KK: return launch_lex_small_k<KK>(d_weight, n_devices, d_binom, h, d_out_mapped, epoch, st);
+    switch (h.k) {
+        TP_CASE(1) TP_CASE(2) TP_CASE(3) TP_CASE(4) TP_CASE(5) TP_CASE(6) TP_CASE(7) TP_CASE(8)
+        TP_CASE(9) TP_CASE(10) TP_CASE(11) TP_CASE(12) TP_CASE(13) TP_CASE(14) TP_CASE(15) TP_CASE(16)
+    }
+#undef TP_CASE
+    return cudaErrorInvalidValue;
 }
 
 template <int K>

@@ -39,6 +39,13 @@ cudaError_t tp_launch_exhaustive_lex(const uint8_t *d_weight, int n_devices, con
                                      unsigned long long hi, const TpScratch &scratch, int sm_count,
                                      cudaStream_t stream, TpLaunchInfo *info);
 
+// Latency path: whole request in ONE block, descriptor by value, winner + flag written to mapped
+// host memory (layout: key.hi, key.lo, scored, flag:u32).  For totals <= TP_FAST_MAX_SUBSETS.
+#define TP_FAST_MAX_SUBSETS 32768
+cudaError_t tp_launch_exhaustive_lex_small(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                           const TpReq &h_rq, void *d_out_mapped, unsigned epoch,
+                                           cudaStream_t stream);
+
 // Family members only: one thread per bitmask over the groups with free devices, masks [lo, hi).
 #define TP_FAMILY_MAX_GROUPS 24
 cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
