@@ -15,8 +15,8 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libtpalloc.so")
-SOURCES = ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "csrc/tp_split_m64.cu", "csrc/tp_split_m96.cu",
-           "csrc/tp_split_m128.cu", "host/besteffort_policy.cpp"]
+SPLIT_UNITS = [f"csrc/tp_split_m{m}_d{d}.cu" for m in (128, 96, 64) for d in (4, 3, 2, 1, 0)]  # slowest first
+SOURCES = SPLIT_UNITS + ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
 HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_device.cuh", "csrc/tp_split.cuh",
            "host/besteffort_policy.h"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]

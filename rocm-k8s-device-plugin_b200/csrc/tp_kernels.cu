@@ -356,15 +356,21 @@ cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, c
                                        int shard_idx, int shard_cnt, const TpScratch &sc, unsigned *d_counter,
                                        int sm_count, cudaStream_t st, TpLaunchInfo *info) {
     const int D = hp.q - 2, need = h.n - hp.p;
-    if (need <= 64)
-        return tp_launch_split_m64(D, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc,
-                                   d_counter, sm_count, st, info);
-    if (need <= 96)
-        return tp_launch_split_m96(D, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc,
-                                   d_counter, sm_count, st, info);
-    if (need <= 128)
-        return tp_launch_split_m128(D, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc,
-                                    d_counter, sm_count, st, info);
+#define TP_SPLIT_ARGS d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc, d_counter, sm_count, st, info
+#define TP_SPLIT_BY_DEPTH(M)                                   \
+    switch (D) {                                               \
+    case 0: return tp_launch_split_m##M##_d0(TP_SPLIT_ARGS);   \
+    case 1: return tp_launch_split_m##M##_d1(TP_SPLIT_ARGS);   \
+    case 2: return tp_launch_split_m##M##_d2(TP_SPLIT_ARGS);   \
+    case 3: return tp_launch_split_m##M##_d3(TP_SPLIT_ARGS);   \
+    case 4: return tp_launch_split_m##M##_d4(TP_SPLIT_ARGS);   \
+    default: return cudaErrorInvalidValue;                     \
+    }
+    if (need <= 64) { TP_SPLIT_BY_DEPTH(64) }
+    if (need <= 96) { TP_SPLIT_BY_DEPTH(96) }
+    if (need <= 128) { TP_SPLIT_BY_DEPTH(128) }
+#undef TP_SPLIT_BY_DEPTH
+#undef TP_SPLIT_ARGS
     return cudaErrorInvalidValue;
 }
 

@@ -22,15 +22,18 @@ cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, c
                                        const TpReq *d_rq, const TpReq &h_rq, const TpPlan *d_plan,
                                        const TpPlan &h_plan, int shard_idx, int shard_cnt, const TpScratch &scratch,
                                        unsigned *d_counter, int sm_count, cudaStream_t stream, TpLaunchInfo *info);
-// per-width launchers, defined in tp_split_m64.cu / tp_split_m96.cu / tp_split_m128.cu (D = q - 2)
-#define TP_DECLARE_SPLIT_LAUNCHER(M)                                                                            \
-    cudaError_t tp_launch_split_m##M(int D, const uint8_t *W, int nd, const unsigned long long *binom,         \
-                                     const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int si, int sn,  \
-                                     const TpScratch &sc, unsigned *d_counter, int sms, cudaStream_t st,       \
-                                     TpLaunchInfo *info);
-TP_DECLARE_SPLIT_LAUNCHER(64)
-TP_DECLARE_SPLIT_LAUNCHER(96)
-TP_DECLARE_SPLIT_LAUNCHER(128)
+// per-instantiation launchers, defined in tp_split_m<M>_d<D>.cu (D = q - 2)
+#define TP_DECLARE_SPLIT_LAUNCHER(M, D)                                                                          \
+    cudaError_t tp_launch_split_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,          \
+                                            const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int si,    \
+                                            int sn, const TpScratch &sc, unsigned *d_counter, int sms,          \
+                                            cudaStream_t st, TpLaunchInfo *info);
+#define TP_DECLARE_SPLIT_LAUNCHERS(M)                                                                  \
+    TP_DECLARE_SPLIT_LAUNCHER(M, 0) TP_DECLARE_SPLIT_LAUNCHER(M, 1) TP_DECLARE_SPLIT_LAUNCHER(M, 2)    \
+    TP_DECLARE_SPLIT_LAUNCHER(M, 3) TP_DECLARE_SPLIT_LAUNCHER(M, 4)
+TP_DECLARE_SPLIT_LAUNCHERS(64)
+TP_DECLARE_SPLIT_LAUNCHERS(96)
+TP_DECLARE_SPLIT_LAUNCHERS(128)
 
 // Score ranks [lo, hi) of the C(n, k') lexicographic subset order of request *rq (device
 // pointer; h_rq is the host copy used for launch geometry) and leave the winner in scratch.out.

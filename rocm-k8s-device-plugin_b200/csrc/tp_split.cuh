@@ -474,18 +474,11 @@ static cudaError_t launch_split_md(const uint8_t *W, int nd, const u64 *binom, c
     return cudaGetLastError();
 }
 
-// One translation unit per M defines this for its M.
-#define TP_DEFINE_SPLIT_LAUNCHER(M)                                                                                  \
-    cudaError_t tp_launch_split_m##M(int D, const uint8_t *W, int nd, const unsigned long long *binom,              \
-                                     const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int si, int sn,       \
-                                     const TpScratch &sc, unsigned *d_counter, int sms, cudaStream_t st,            \
-                                     TpLaunchInfo *info) {                                                          \
-        switch (D) {                                                                                                 \
-        case 0: return launch_split_md<M, 0>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);   \
-        case 1: return launch_split_md<M, 1>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);   \
-        case 2: return launch_split_md<M, 2>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);   \
-        case 3: return launch_split_md<M, 3>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);   \
-        case 4: return launch_split_md<M, 4>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);   \
-        }                                                                                                            \
-        return cudaErrorInvalidValue;                                                                                \
+// One translation unit per (M, D) defines this for its instantiation.
+#define TP_DEFINE_SPLIT_LAUNCHER(M, D)                                                                           \
+    cudaError_t tp_launch_split_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,          \
+                                            const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int si,    \
+                                            int sn, const TpScratch &sc, unsigned *d_counter, int sms,          \
+                                            cudaStream_t st, TpLaunchInfo *info) {                              \
+        return launch_split_md<M, D>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);       \
     }
