@@ -301,6 +301,7 @@ def main():
         if world == 1 and not args.no_extra:
             line["latency"] = latency_leg(tp, dev)
             line["c3"] = c3_leg(tp)
+            line["c5_pod_storm"] = pod_storm_leg(tp)
         if world == 1 and not args.no_cpu:
             from oracle.binding import RefPolicy
             ref = RefPolicy()
@@ -357,6 +358,49 @@ def latency_leg(tp, dev):
         pol.close()
     out["note"] = "wall clock around the call (python ctypes overhead included in all three columns)"
     return out
+
+
+def pod_storm_leg(tp, count=10000):
+    """BASELINE config C5: 10 000 requests with random availability masks over the CPX topology
+    (SURVEY 8d generator, splitmix64 seed 0x5EED0001), answered by ONE tp_allocate_batch call."""
+    import topo
+    from oracle.binding import RefPolicy
+    devs, pairs = topo.fixture_topology("cpx")
+    ids = [d.Id for d in devs]
+    gen = topo.SplitMix64(0x5EED0001)
+    reqs = []
+    while len(reqs) < count:
+        p = (0.25, 0.5, 0.75)[gen.below(3)]
+        av = [i for i in ids if gen.chance(p)]
+        k = (1, 2, 4, 8)[gen.below(4)]
+        if len(av) < k:
+            continue
+        reqs.append((av, [av[gen.below(len(av))]] if gen.chance(0.2) else [], k))
+    pol = tp.BestEffortPolicy(cuda_device=0)
+    pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+    batch = tp.Batch(pol, reqs)
+    batch.run()  # warm-up (buffers grow here)
+    times = []
+    for _ in range(3):
+        t = time.perf_counter()
+        batch.run()
+        times.append(time.perf_counter() - t)
+    got, infos = batch.results()
+    ref = RefPolicy()
+    ref.InitPairs(devs, pairs)
+    t = time.perf_counter()
+    want = [ref.Allocate(*r) for r in reqs]
+    cpu_s = time.perf_counter() - t
+    assert got == want
+    subsets = sum(i["subsets_scored"] for i in infos)
+    best = min(times)
+    pol.close()
+    return {"requests": count, "batch_ms": best * 1e3, "requests_per_s": count / best,
+            "subsets_scored": subsets, "subsets_per_s": subsets / best,
+            "gpu_launches": max(i["gpu_launches"] for i in infos),
+            "cpu_reference_bfs_requests_per_s": count / cpu_s,
+            "note": "wall clock around tp_allocate_batch (host prepare + H2D + kernels + D2H + decode); "
+                    "cpu column = oracle BFS restatement, 1 thread, python call overhead included"}
 
 
 def c3_leg(tp):

@@ -333,30 +333,45 @@ def measure_int_peak(cuda_device=0, variant=0) -> float:
     return g.value
 
 
+class Batch:
+    """Marshalled arguments of one tp_allocate_batch call (built once, callable many times)."""
+
+    def __init__(self, pol: BestEffortPolicy, requests):
+        self.pol, self.n = pol, len(requests)
+        self.arr = (TpRequest * max(self.n, 1))()
+        self._keep = []
+        self.stride = max([r[2] for r in requests] + [1])
+        for i, (av, rq, size) in enumerate(requests):
+            a, r = _i32(pol.indices(av)), _i32(pol.indices(rq or []))
+            self._keep.append((a, r))
+            self.arr[i] = TpRequest(a, len(av), r, len(rq or []), size)
+        self.out = (C.c_int32 * (max(self.n, 1) * self.stride))()
+        self.status = (C.c_int32 * max(self.n, 1))()
+        self.infos = (TpResult * max(self.n, 1))()
+
+    def run(self):
+        rc = lib().tp_allocate_batch(self.pol.handle, self.n, self.arr, self.out, self.stride, self.status,
+                                     self.infos)
+        if rc < 0:
+            raise AllocatorError(rc, strerror(rc))
+
+    def results(self):
+        res = []
+        for i in range(self.n):
+            st = self.status[i]
+            if st < 0:
+                res.append(AllocatorError(st, strerror(st)))
+            else:
+                res.append([self.pol.devices[j].Id for j in self.out[i * self.stride:i * self.stride + st]])
+        return res, [self.infos[i].dict() for i in range(self.n)]
+
+
 def allocate_batch(pol: BestEffortPolicy, requests):
     """tp_allocate_batch: requests = [(available ids, required ids, size)], the ContainerRequests of
     one GetPreferredAllocation RPC (amdgpu.go:307-317).  Returns ([ids] or AllocatorError per request, infos)."""
-    n = len(requests)
-    arr = (TpRequest * max(n, 1))()
-    keep = []
-    stride = max([r[2] for r in requests] + [1])
-    for i, (av, rq, size) in enumerate(requests):
-        a, r = _i32(pol.indices(av)), _i32(pol.indices(rq or []))
-        keep.append((a, r))
-        arr[i] = TpRequest(a, len(av), r, len(rq or []), size)
-    out = (C.c_int32 * (max(n, 1) * stride))()
-    status = (C.c_int32 * max(n, 1))()
-    infos = (TpResult * max(n, 1))()
-    rc = lib().tp_allocate_batch(pol.handle, n, arr, out, stride, status, infos)
-    if rc < 0:
-        raise AllocatorError(rc, strerror(rc))
-    res = []
-    for i in range(n):
-        if status[i] < 0:
-            res.append(AllocatorError(status[i], strerror(status[i])))
-        else:
-            res.append([pol.devices[j].Id for j in out[i * stride:i * stride + status[i]]])
-    return res, [infos[i].dict() for i in range(n)]
+    b = Batch(pol, requests)
+    b.run()
+    return b.results()
 
 
 def build_weights(group, numa_node, link_type, cuda_device=0):

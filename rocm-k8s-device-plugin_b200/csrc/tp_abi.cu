@@ -14,6 +14,7 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "tp_kernels.cuh"
@@ -77,6 +78,17 @@ struct tp_policy {
     std::mutex mu;
     std::condition_variable cv;
     std::string last_cuda_error;
+    // tp_allocate_batch: one batch at a time per policy; buffers grow on demand
+    struct Batch {
+        std::mutex mu;
+        cudaStream_t stream = nullptr;
+        size_t cap_reqs = 0, cap_plans = 0;
+        TpReq *h_reqs = nullptr, *d_reqs = nullptr;
+        TpPlan *h_plans = nullptr, *d_plans = nullptr;
+        TpBatchEntry *h_order = nullptr, *d_order = nullptr;
+        TpBatchOut *h_results = nullptr, *d_results = nullptr;
+        unsigned *d_grab = nullptr; // one counter per kernel group
+    } batch;
 };
 
 namespace {
@@ -148,6 +160,19 @@ int init_ctx(tp_policy *p, Ctx &c) {
     c.scratch.ticket = (unsigned int *)(tail + 40);
     c.d_counter = (unsigned *)(tail + 48);
     return 0;
+}
+
+void batch_release(tp_policy::Batch &b) {
+    if (b.h_reqs) cudaFreeHost(b.h_reqs);
+    if (b.h_plans) cudaFreeHost(b.h_plans);
+    if (b.h_order) cudaFreeHost(b.h_order);
+    if (b.h_results) cudaFreeHost(b.h_results);
+    if (b.d_reqs) cudaFree(b.d_reqs);
+    if (b.d_plans) cudaFree(b.d_plans);
+    if (b.d_order) cudaFree(b.d_order);
+    if (b.d_results) cudaFree(b.d_results);
+    if (b.d_grab) cudaFree(b.d_grab);
+    if (b.stream) cudaStreamDestroy(b.stream);
 }
 
 void free_ctx(Ctx &c) {
@@ -603,6 +628,7 @@ void tp_destroy(tp_policy *p) {
     {
         DeviceGuard guard(p->cuda_device);
         for (Ctx &c : p->ctxs) free_ctx(c);
+        batch_release(p->batch);
         if (p->d_weight) cudaFree(p->d_weight);
         if (p->d_binom) cudaFree(p->d_binom);
     }
@@ -630,14 +656,187 @@ int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32
     return decode(pr, key, req, out);
 }
 
+namespace {
+
+constexpr int kBatchMaxGroups = 64;
+
+int batch_reserve(tp_policy *p, size_t n_reqs, size_t n_plans) {
+    tp_policy::Batch &b = p->batch;
+    if (!b.stream) {
+        TP_CUDA(p, cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
+        TP_CUDA(p, cudaMalloc((void **)&b.d_grab, kBatchMaxGroups * sizeof(unsigned)));
+    }
+    if (n_reqs > b.cap_reqs) {
+        const size_t cap = std::max<size_t>(n_reqs, 256) * 5 / 4;
+        if (b.h_reqs) cudaFreeHost(b.h_reqs);
+        if (b.h_order) cudaFreeHost(b.h_order);
+        if (b.h_results) cudaFreeHost(b.h_results);
+        if (b.d_reqs) cudaFree(b.d_reqs);
+        if (b.d_order) cudaFree(b.d_order);
+        if (b.d_results) cudaFree(b.d_results);
+        b.h_reqs = nullptr; b.h_order = nullptr; b.h_results = nullptr;
+        b.d_reqs = nullptr; b.d_order = nullptr; b.d_results = nullptr;
+        b.cap_reqs = 0;
+        TP_CUDA(p, cudaHostAlloc((void **)&b.h_reqs, cap * sizeof(TpReq), cudaHostAllocDefault));
+        TP_CUDA(p, cudaHostAlloc((void **)&b.h_order, cap * sizeof(TpBatchEntry), cudaHostAllocDefault));
+        TP_CUDA(p, cudaHostAlloc((void **)&b.h_results, cap * sizeof(TpBatchOut), cudaHostAllocDefault));
+        TP_CUDA(p, cudaMalloc((void **)&b.d_reqs, cap * sizeof(TpReq)));
+        TP_CUDA(p, cudaMalloc((void **)&b.d_order, cap * sizeof(TpBatchEntry)));
+        TP_CUDA(p, cudaMalloc((void **)&b.d_results, cap * sizeof(TpBatchOut)));
+        b.cap_reqs = cap;
+    }
+    if (n_plans > b.cap_plans) {
+        const size_t cap = std::max<size_t>(n_plans, 64) * 5 / 4;
+        if (b.h_plans) cudaFreeHost(b.h_plans);
+        if (b.d_plans) cudaFree(b.d_plans);
+        b.h_plans = nullptr; b.d_plans = nullptr;
+        b.cap_plans = 0;
+        TP_CUDA(p, cudaHostAlloc((void **)&b.h_plans, cap * sizeof(TpPlan), cudaHostAllocDefault));
+        TP_CUDA(p, cudaMalloc((void **)&b.d_plans, cap * sizeof(TpPlan)));
+        b.cap_plans = cap;
+    }
+    return 0;
+}
+
+struct BatchGroup {
+    int kernel, a, b, c; // LEX: (k', -, -); SPLIT: (p, q, lane-vector class)
+    int max_n = 0, max_k = 0;
+    std::vector<int> members; // request indices
+};
+
+} // namespace
+
+// All requests of one RPC in a handful of launches: requests are prepared on the host (in
+// parallel), grouped by the kernel instantiation they need, and each group runs as ONE persistent
+// launch in which a block owns a whole request (heaviest first).  Requests the reference answers
+// without searching never reach the GPU; the rare ones outside the batch kernels (Family-only)
+// go through tp_allocate.
 int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, int32_t *out, int32_t out_stride,
                       int32_t *status, tp_result *infos) {
     if (!p || n_requests < 0 || (n_requests && (!rqs || !out || !status))) return TP_ERR_BAD_ARGUMENT;
+    if (n_requests < 4 || p->host_only) { // not worth a batch: answer one by one
+        for (int i = 0; i < n_requests; i++) {
+            if (rqs[i].size > out_stride) { status[i] = TP_ERR_BAD_ARGUMENT; continue; }
+            status[i] = tp_allocate(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required,
+                                    rqs[i].size, out + (size_t)i * out_stride, infos ? infos + i : nullptr);
+        }
+        return TP_OK;
+    }
+    std::vector<Prep> preps(n_requests);
+    {
+        const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_requests / 64 + 1));
+        auto work = [&](int t) {
+            for (int i = t; i < n_requests; i += nthreads)
+                prepare(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required, rqs[i].size,
+                        preps[i]);
+        };
+        std::vector<std::thread> pool;
+        for (int t = 1; t < nthreads; t++) pool.emplace_back(work, t);
+        work(0);
+        for (std::thread &t : pool) t.join();
+    }
+    std::vector<BatchGroup> groups;
+    std::vector<int> singles; // served by tp_allocate after the batch
+    size_t n_plans = 0;
     for (int i = 0; i < n_requests; i++) {
-        if (rqs[i].size > out_stride) { status[i] = TP_ERR_BAD_ARGUMENT; continue; }
+        const Prep &pr = preps[i];
+        if (infos) memset(&infos[i], 0, sizeof(tp_result));
+        if (rqs[i].size > out_stride && !pr.status) { status[i] = TP_ERR_BAD_ARGUMENT; continue; }
+        if (pr.status) { status[i] = pr.status; continue; }
+        if (pr.shortcut) {
+            memcpy(out + (size_t)i * out_stride, pr.shortcut == 1 ? rqs[i].available : rqs[i].required,
+                   sizeof(int32_t) * rqs[i].size);
+            status[i] = rqs[i].size;
+            continue;
+        }
+        if (pr.family_only || pr.kernel == TP_KERNEL_FAMILY) { singles.push_back(i); continue; }
+        BatchGroup key;
+        key.kernel = pr.kernel;
+        if (pr.kernel == TP_KERNEL_SPLIT) {
+            const int need = pr.rq.n - pr.plan.p;
+            key.a = pr.plan.p; key.b = pr.plan.q; key.c = need <= 64 ? 64 : need <= 96 ? 96 : 128;
+            n_plans++;
+        } else {
+            key.a = pr.rq.k; key.b = 0; key.c = 0;
+        }
+        size_t g = 0;
+        for (; g < groups.size(); g++)
+            if (groups[g].kernel == key.kernel && groups[g].a == key.a && groups[g].b == key.b && groups[g].c == key.c) break;
+        if (g == groups.size()) {
+            if ((int)groups.size() == kBatchMaxGroups) { singles.push_back(i); if (pr.kernel == TP_KERNEL_SPLIT) n_plans--; continue; }
+            groups.push_back(key);
+        }
+        groups[g].members.push_back(i);
+        groups[g].max_n = std::max(groups[g].max_n, pr.rq.n);
+        groups[g].max_k = std::max(groups[g].max_k, pr.rq.k);
+    }
+    int launches = 0;
+    if (!groups.empty()) {
+        std::lock_guard<std::mutex> batch_lock(p->batch.mu);
+        DeviceGuard guard(p->cuda_device);
+        int rc = batch_reserve(p, (size_t)n_requests, n_plans);
+        if (rc) return rc;
+        tp_policy::Batch &b = p->batch;
+        size_t n_order = 0, plan_at = 0;
+        std::vector<size_t> first(groups.size());
+        for (size_t g = 0; g < groups.size(); g++) {
+            BatchGroup &grp = groups[g];
+            std::sort(grp.members.begin(), grp.members.end(),
+                      [&](int x, int y) { return preps[x].rq.total > preps[y].rq.total; }); // heaviest first
+            first[g] = n_order;
+            for (int i : grp.members) {
+                b.h_reqs[i] = preps[i].rq;
+                TpBatchEntry e{i, 0};
+                if (grp.kernel == TP_KERNEL_SPLIT) {
+                    b.h_plans[plan_at] = preps[i].plan;
+                    e.plan = (int32_t)plan_at++;
+                }
+                b.h_order[n_order++] = e;
+            }
+        }
+        TP_CUDA(p, cudaMemcpyAsync(b.d_reqs, b.h_reqs, (size_t)n_requests * sizeof(TpReq), cudaMemcpyHostToDevice, b.stream));
+        if (plan_at)
+            TP_CUDA(p, cudaMemcpyAsync(b.d_plans, b.h_plans, plan_at * sizeof(TpPlan), cudaMemcpyHostToDevice, b.stream));
+        TP_CUDA(p, cudaMemcpyAsync(b.d_order, b.h_order, n_order * sizeof(TpBatchEntry), cudaMemcpyHostToDevice, b.stream));
+        for (size_t g = 0; g < groups.size(); g++) {
+            const BatchGroup &grp = groups[g];
+            TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + g, (int32_t)grp.members.size(), 0};
+            TpLaunchInfo li{};
+            if (grp.kernel == TP_KERNEL_SPLIT)
+                TP_CUDA(p, tp_launch_batch_split(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
+                                                 grp.max_n, grp.max_k, tb, p->sm_count, b.stream, &li));
+            else
+                TP_CUDA(p, tp_launch_batch_lex(p->d_weight, p->n, p->d_binom, b.d_reqs, grp.a, grp.max_n, tb,
+                                               p->sm_count, b.stream, &li));
+            launches += li.launches;
+        }
+        TP_CUDA(p, cudaMemcpyAsync(b.h_results, b.d_results, (size_t)n_requests * sizeof(TpBatchOut),
+                                   cudaMemcpyDeviceToHost, b.stream));
+        TP_CUDA(p, cudaStreamSynchronize(b.stream));
+        for (const BatchGroup &grp : groups)
+            for (int i : grp.members) {
+                const TpKey key = b.h_results[i].key;
+                status[i] = decode(preps[i], key, rqs[i].required, out + (size_t)i * out_stride);
+                if (infos) {
+                    tp_result &r = infos[i];
+                    r.searched = 1;
+                    r.kernel = preps[i].kernel;
+                    r.subsets_scored = b.h_results[i].scored;
+                    r.subsets_total = preps[i].rq.total;
+                    r.gpu_launches = launches; // launches of the whole batch (shared by its requests)
+                    r.key.hi = key.hi;
+                    r.key.lo = key.lo;
+                    if (key.hi != TP_KEY_INF_HI) {
+                        r.score = tp_key_score(key);
+                        r.groups_touched = tp_key_groups(key);
+                    }
+                }
+            }
+    }
+    for (int i : singles)
         status[i] = tp_allocate(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required,
                                 rqs[i].size, out + (size_t)i * out_stride, infos ? infos + i : nullptr);
-    }
     return TP_OK;
 }
 

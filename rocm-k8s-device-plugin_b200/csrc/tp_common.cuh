@@ -95,6 +95,25 @@ struct TpScratch {
 
 #define TP_MAX_BLOCKS 4096
 
+// Batch mode (tp_allocate_batch): one block per request.  `slot` indexes the batch's request and
+// result arrays, `plan` the (SPLIT-only) plan array.
+struct TpBatchEntry {
+    int32_t slot;
+    int32_t plan;
+};
+struct TpBatchOut {
+    TpKey key;
+    unsigned long long scored;
+    unsigned long long pad;
+};
+struct TpBatch { // count == 0: single-request mode (all blocks share request 0, cross-block finish)
+    const TpBatchEntry *order;
+    TpBatchOut *results;
+    unsigned *grab; // next entry of `order` to hand out
+    int32_t count;
+    int32_t pad;
+};
+
 // ---- kernel SPLIT (tp_split.cuh): constants and the host-built work plan ----------------------
 #define TP_BIG 0x3000u
 #define TP_BIG2 0x30003000u

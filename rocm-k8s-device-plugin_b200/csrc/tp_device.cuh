@@ -110,6 +110,35 @@ static __device__ void tp_block_finish(TpKey best, u64 counted, const TpScratch 
     }
 }
 
+// Block-wide (min key, sum count); the result is valid in thread 0.  Ends with a __syncthreads,
+// so shared memory may be reused right after.
+static __device__ void tp_block_reduce(TpKey &best, u64 &counted) {
+    __shared__ TpKey s_red[32];
+    __shared__ u64 s_cnt[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    best = tp_warp_min_key(best);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) counted += __shfl_xor_sync(0xFFFFFFFFu, counted, off);
+    if (lane == 0) {
+        s_red[warp] = best;
+        s_cnt[warp] = counted;
+    }
+    __syncthreads();
+    if (warp == 0) {
+        TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+        u64 c = 0;
+        if (lane < nwarps) {
+            k = s_red[lane];
+            c = s_cnt[lane];
+        }
+        best = tp_warp_min_key(k);
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
+        counted = c;
+    }
+    __syncthreads();
+}
+
 // Stage the request into shared memory: pair weights in canonical order, the unary term
 // u[x] = sum over required r of W[x][r], and the group tables.  Returns the seed bound:
 // the score of canonical positions {0..k-1}, which is always a Family member.

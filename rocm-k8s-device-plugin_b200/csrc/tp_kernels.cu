@@ -21,14 +21,13 @@
 template <int K>
 __device__ __forceinline__ void tp_lex_body(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
                                             const TpReq *__restrict__ rq, u64 lo, u64 hi, u64 per_thread,
-                                            TpKey &best, u64 &counted) {
+                                            u64 gtid, TpKey &best, u64 &counted) {
     extern __shared__ __align__(16) unsigned char smem[];
     __shared__ int s_bound;
     const int n = rq->n;
     const TpSmem s = tp_smem_carve(smem, n, K);
     tp_stage_request(s, W, nd, binom_g, rq, K, &s_bound);
     const int stride = s.stride, dbits = rq->dbits;
-    const u64 gtid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     u64 my_lo = lo + gtid * per_thread;
     if (my_lo < hi) {
         u64 remaining = (hi - my_lo < per_thread) ? hi - my_lo : per_thread;
@@ -106,14 +105,75 @@ __device__ __forceinline__ void tp_lex_body(const uint8_t *__restrict__ W, int n
     }
 }
 
+// Single request (batch.count == 0): the grid splits the rank range, the last block reduces the
+// partials.  Batch: every block takes whole requests off batch.order and ranks them alone.
 template <int K>
 __global__ void __launch_bounds__(TP_LEX_THREADS)
 tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
-                  const TpReq *__restrict__ rq, u64 lo, u64 hi, u64 per_thread, TpScratch sc) {
-    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
-    u64 counted = 0;
-    tp_lex_body<K>(W, nd, binom_g, rq, lo, hi, per_thread, best, counted);
-    tp_block_finish(best, counted, sc);
+                  const TpReq *__restrict__ reqs, u64 lo, u64 hi, u64 per_thread, TpScratch sc, TpBatch batch) {
+    __shared__ unsigned s_entry;
+    for (int iter = 0;; iter++) {
+        const TpReq *rq = reqs;
+        u64 gtid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+        int slot = 0;
+        if (batch.count > 0) {
+            __syncthreads(); // everybody is done with the previous request's shared memory
+            if (threadIdx.x == 0) s_entry = atomicAdd(batch.grab, 1u);
+            __syncthreads();
+            if (s_entry >= (unsigned)batch.count) break;
+            slot = batch.order[s_entry].slot;
+            rq = reqs + slot;
+            lo = 0;
+            hi = rq->total;
+            per_thread = (hi + blockDim.x - 1) / blockDim.x;
+            gtid = threadIdx.x;
+        } else if (iter > 0) {
+            break;
+        }
+        TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+        u64 counted = 0;
+        tp_lex_body<K>(W, nd, binom_g, rq, lo, hi, per_thread, gtid, best, counted);
+        if (batch.count > 0) {
+            tp_block_reduce(best, counted);
+            if (threadIdx.x == 0) {
+                batch.results[slot].key = best;
+                batch.results[slot].scored = counted;
+            }
+        } else {
+            tp_block_finish(best, counted, sc);
+        }
+    }
+}
+
+template <int K>
+static cudaError_t launch_batch_lex_k(const uint8_t *W, int nd, const u64 *binom, const TpReq *d_reqs, int max_n,
+                                      const TpBatch &batch, int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+    cudaError_t e = cudaMemsetAsync(batch.grab, 0, sizeof(unsigned), st);
+    if (e != cudaSuccess) return e;
+    int blocks = sm_count * 4;
+    if (batch.count < blocks) blocks = batch.count;
+    TpScratch none{};
+    tp_exhaustive_lex<K><<<blocks, TP_LEX_THREADS, tp_smem_bytes(max_n, K), st>>>(W, nd, binom, d_reqs, 0, 0, 0, none,
+                                                                                batch);
+    if (info) {
+        info->launches = 1;
+        info->blocks = blocks;
+        info->threads = TP_LEX_THREADS;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t tp_launch_batch_lex(const uint8_t *d_weight, int n_devices, const u64 *d_binom, const TpReq *d_reqs,
+                                int k, int max_n, const TpBatch &batch, int sm_count, cudaStream_t st,
+                                TpLaunchInfo *info) {
+#define TP_CASE(KK) \
+    case KK: return launch_batch_lex_k<KK>(d_weight, n_devices, d_binom, d_reqs, max_n, batch, sm_count, st, info);
+    switch (k) {
+        TP_CASE(1) TP_CASE(2) TP_CASE(3) TP_CASE(4) TP_CASE(5) TP_CASE(6) TP_CASE(7) TP_CASE(8)
+        TP_CASE(9) TP_CASE(10) TP_CASE(11) TP_CASE(12) TP_CASE(13) TP_CASE(14) TP_CASE(15) TP_CASE(16)
+    }
+#undef TP_CASE
+    return cudaErrorInvalidValue;
 }
 
 // Latency path (the 28- and 70-subset requests of BASELINE configs C1/C2): one block, the
@@ -136,7 +196,7 @@ tp_exhaustive_lex_small(const uint8_t *__restrict__ W, int nd, const u64 *__rest
     __shared__ u64 s_cnt[32];
     TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
     u64 counted = 0;
-    tp_lex_body<K>(W, nd, binom_g, &rq, lo, hi, per_thread, best, counted);
+    tp_lex_body<K>(W, nd, binom_g, &rq, lo, hi, per_thread, (u64)threadIdx.x, best, counted);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
     best = tp_warp_min_key(best);
 #pragma unroll
@@ -210,7 +270,8 @@ static cudaError_t launch_lex_k(const uint8_t *W, int nd, const u64 *binom, cons
         per_thread = (span + blocks * block - 1) / (blocks * block);
     }
     const size_t smem = tp_smem_bytes(h.n, K);
-    tp_exhaustive_lex<K><<<(unsigned)blocks, block, smem, st>>>(W, nd, binom, d_rq, lo, hi, per_thread, sc);
+    TpBatch single{};
+    tp_exhaustive_lex<K><<<(unsigned)blocks, block, smem, st>>>(W, nd, binom, d_rq, lo, hi, per_thread, sc, single);
     if (info) {
         info->launches = 1;
         info->blocks = (int)blocks;
@@ -351,12 +412,12 @@ cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const u64 *
 }
 
 // Kernel SPLIT: pick the narrowest lane vector that holds every pivot (n - p positions).
-cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, const u64 *d_binom,
-                                       const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, const TpPlan &hp,
-                                       int shard_idx, int shard_cnt, const TpScratch &sc, unsigned *d_counter,
-                                       int sm_count, cudaStream_t st, TpLaunchInfo *info) {
-    const int D = hp.q - 2, need = h.n - hp.p;
-#define TP_SPLIT_ARGS d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc, d_counter, sm_count, st, info
+static cudaError_t tp_dispatch_split(int D, int need, const uint8_t *d_weight, int n_devices, const u64 *d_binom,
+                                     const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int shard_idx,
+                                     int shard_cnt, const TpScratch &sc, unsigned *d_counter, int sm_count,
+                                     cudaStream_t st, TpLaunchInfo *info, const TpBatch &batch) {
+#define TP_SPLIT_ARGS \
+    d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx, shard_cnt, sc, d_counter, sm_count, st, info, batch
 #define TP_SPLIT_BY_DEPTH(M)                                   \
     switch (D) {                                               \
     case 0: return tp_launch_split_m##M##_d0(TP_SPLIT_ARGS);   \
@@ -372,6 +433,26 @@ cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, c
 #undef TP_SPLIT_BY_DEPTH
 #undef TP_SPLIT_ARGS
     return cudaErrorInvalidValue;
+}
+
+cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, const u64 *d_binom,
+                                       const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, const TpPlan &hp,
+                                       int shard_idx, int shard_cnt, const TpScratch &sc, unsigned *d_counter,
+                                       int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+    TpBatch single{};
+    return tp_dispatch_split(hp.q - 2, h.n - hp.p, d_weight, n_devices, d_binom, d_rq, h, d_plan, shard_idx,
+                             shard_cnt, sc, d_counter, sm_count, st, info, single);
+}
+
+cudaError_t tp_launch_batch_split(const uint8_t *d_weight, int n_devices, const u64 *d_binom, const TpReq *d_reqs,
+                                  const TpPlan *d_plans, int p, int q, int max_n, int max_k, const TpBatch &batch,
+                                  int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+    TpReq h{};
+    h.n = max_n; // sizes the shared memory for the largest request of the group
+    h.k = max_k;
+    TpScratch none{};
+    return tp_dispatch_split(q - 2, max_n - p, d_weight, n_devices, d_binom, d_reqs, h, d_plans, 0, 1, none,
+                             nullptr, sm_count, st, info, batch);
 }
 
 // ---------------------------------------------------------------------------------------

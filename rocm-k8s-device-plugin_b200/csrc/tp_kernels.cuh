@@ -22,12 +22,20 @@ cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, c
                                        const TpReq *d_rq, const TpReq &h_rq, const TpPlan *d_plan,
                                        const TpPlan &h_plan, int shard_idx, int shard_cnt, const TpScratch &scratch,
                                        unsigned *d_counter, int sm_count, cudaStream_t stream, TpLaunchInfo *info);
+// Batch mode: one block per request of `batch.order`; d_reqs / d_plans are the batch arrays, (p, q,
+// max_n, max_k) describe the group (all its requests share p and q, hence the instantiation).
+cudaError_t tp_launch_batch_split(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                  const TpReq *d_reqs, const TpPlan *d_plans, int p, int q, int max_n, int max_k,
+                                  const TpBatch &batch, int sm_count, cudaStream_t stream, TpLaunchInfo *info);
+cudaError_t tp_launch_batch_lex(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                const TpReq *d_reqs, int k, int max_n, const TpBatch &batch, int sm_count,
+                                cudaStream_t stream, TpLaunchInfo *info);
 // per-instantiation launchers, defined in tp_split_m<M>_d<D>.cu (D = q - 2)
 #define TP_DECLARE_SPLIT_LAUNCHER(M, D)                                                                          \
     cudaError_t tp_launch_split_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,          \
                                             const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int si,    \
                                             int sn, const TpScratch &sc, unsigned *d_counter, int sms,          \
-                                            cudaStream_t st, TpLaunchInfo *info);
+                                            cudaStream_t st, TpLaunchInfo *info, const TpBatch &batch);
 #define TP_DECLARE_SPLIT_LAUNCHERS(M)                                                                  \
     TP_DECLARE_SPLIT_LAUNCHER(M, 0) TP_DECLARE_SPLIT_LAUNCHER(M, 1) TP_DECLARE_SPLIT_LAUNCHER(M, 2)    \
     TP_DECLARE_SPLIT_LAUNCHER(M, 3) TP_DECLARE_SPLIT_LAUNCHER(M, 4)

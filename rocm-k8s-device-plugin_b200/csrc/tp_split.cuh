@@ -264,11 +264,14 @@ struct TpSplitWalk {
     }
 };
 
+// The search of one request by the calling block: items are handed out through *work_counter
+// (a global word shared by the grid, or a shared-memory word when the block owns the request).
+// Not inlined on purpose: the kernel's request loop must not compete with it for registers.
 template <int M, int D>
-__global__ void __launch_bounds__(TP_SPLIT_THREADS, 2)
-tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
-                    const TpReq *__restrict__ rq, const TpPlan *__restrict__ plan, int shard_idx, int shard_cnt,
-                    TpScratch sc, unsigned *work_counter) {
+__device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int nd,
+                                                const u64 *__restrict__ binom_g, const TpReq *__restrict__ rq,
+                                                const TpPlan *__restrict__ plan, int shard_idx, int shard_cnt,
+                                                unsigned *work_counter, TpKey &best, u64 &counted) {
     using Cfg = TpSplitCfg<M>;
     unsigned char *const smem = tp_split_smem;
     __shared__ int s_bound;
@@ -329,8 +332,6 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
     __syncthreads();
     TpSplitShared sh{wp, wm, n, k, p, q, rq->dbits, rsp, plan->min_w};
     const int c_req = rq->c_req;
-    TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
-    u64 counted = 0;
     const int kcols = k + 1;
     auto C = [&](int a, int b) -> u64 { return (b < 0 || a < b) ? 0ull : s.binom[a * kcols + b]; };
     TpSplitWarp wst{tstack, va, bstack, 0, 0, 0, lane};
@@ -443,7 +444,46 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
         }
         __syncwarp();
     }
-    tp_block_finish(best, counted, sc); // the work counter is re-armed by the launcher's memset
+}
+
+// Single request (batch.count == 0): the whole grid shares the request and its item counter, the
+// last block reduces the partials.  Batch: every block takes whole requests off batch.order.
+template <int M, int D>
+__global__ void __launch_bounds__(TP_SPLIT_THREADS, 2)
+tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
+                    const TpReq *__restrict__ reqs, const TpPlan *__restrict__ plans, int shard_idx, int shard_cnt,
+                    TpScratch sc, unsigned *work_counter, TpBatch batch) {
+    __shared__ unsigned s_entry, s_items;
+    for (int iter = 0;; iter++) {
+        int slot = 0, plan = 0;
+        unsigned *wc = work_counter;
+        if (batch.count > 0) {
+            __syncthreads(); // everybody is done with the previous request's shared memory
+            if (threadIdx.x == 0) {
+                s_entry = atomicAdd(batch.grab, 1u);
+                s_items = 0;
+            }
+            __syncthreads();
+            if (s_entry >= (unsigned)batch.count) break;
+            slot = batch.order[s_entry].slot;
+            plan = batch.order[s_entry].plan;
+            wc = &s_items;
+        } else if (iter > 0) {
+            break;
+        }
+        TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+        u64 counted = 0;
+        tp_split_search<M, D>(W, nd, binom_g, reqs + slot, plans + plan, shard_idx, shard_cnt, wc, best, counted);
+        if (batch.count > 0) {
+            tp_block_reduce(best, counted);
+            if (threadIdx.x == 0) {
+                batch.results[slot].key = best;
+                batch.results[slot].scored = counted;
+            }
+        } else {
+            tp_block_finish(best, counted, sc); // the work counter is re-armed by the launcher's memset
+        }
+    }
 }
 
 static size_t tp_split_smem_bytes(int n, int k, int M, int D) {
@@ -453,19 +493,22 @@ static size_t tp_split_smem_bytes(int n, int k, int M, int D) {
     return off;
 }
 
+// h describes the request (single mode) or carries the largest n and k of the batch (batch mode).
 template <int M, int D>
 static cudaError_t launch_split_md(const uint8_t *W, int nd, const u64 *binom, const TpReq *d_rq, const TpReq &h,
                                    const TpPlan *d_plan, int shard_idx, int shard_cnt, const TpScratch &sc,
-                                   unsigned *d_counter, int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+                                   unsigned *d_counter, int sm_count, cudaStream_t st, TpLaunchInfo *info,
+                                   const TpBatch &batch) {
     const size_t smem = tp_split_smem_bytes(h.n, h.k, M, D);
     cudaError_t e = cudaFuncSetAttribute(tp_exhaustive_split<M, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(d_counter, 0, sizeof(unsigned), st);
+    e = cudaMemsetAsync(batch.count > 0 ? batch.grab : d_counter, 0, sizeof(unsigned), st);
     if (e != cudaSuccess) return e;
-    const int blocks = sm_count * 2;
+    int blocks = sm_count * 2;
+    if (batch.count > 0 && batch.count < blocks) blocks = batch.count;
     tp_exhaustive_split<M, D><<<blocks, TP_SPLIT_THREADS, smem, st>>>(W, nd, binom, d_rq, d_plan, shard_idx,
-                                                                      shard_cnt, sc, d_counter);
+                                                                      shard_cnt, sc, d_counter, batch);
     if (info) {
         info->launches = 1;
         info->blocks = blocks;
@@ -479,6 +522,6 @@ static cudaError_t launch_split_md(const uint8_t *W, int nd, const u64 *binom, c
     cudaError_t tp_launch_split_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,          \
                                             const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int si,    \
                                             int sn, const TpScratch &sc, unsigned *d_counter, int sms,          \
-                                            cudaStream_t st, TpLaunchInfo *info) {                              \
-        return launch_split_md<M, D>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info);       \
+                                            cudaStream_t st, TpLaunchInfo *info, const TpBatch &batch) {        \
+        return launch_split_md<M, D>(W, nd, binom, d_rq, h, d_plan, si, sn, sc, d_counter, sms, st, info, batch); \
     }
