@@ -264,7 +264,7 @@ def main():
         k_ms /= max(args.steps, 3)
         shard_subsets = prep.subsets
         if info["kernel"] == tp.KERNEL_SPLIT:
-            h2d += 3352  # the work plan (TpPlan) travels with the request descriptor
+            h2d += 1176  # the work plan (TpPlan) travels with the request descriptor
         peak_iadd = tp.measure_int_peak(local_rank, 0)      # IADD3, 32-bit lane-ops/s (x1e9)
         peak_addmin = tp.measure_int_peak(local_rank, 3)    # VIADDMNMX.U16x2 lane-instr/s (x1e9)
         rate = shard_subsets / (k_ms * 1e-3)

@@ -227,27 +227,8 @@ bool build_plan(const tp_policy *p, Prep &out) {
         const u64 na = p->binom[n - 1 - jt][pp - 1];
         const u64 chunks = (na + 31) / 32;
         if (chunks == 0 || chunks > 0xFFFFFFFFull) return false;
-        int np = 1;
-        pl.cuts[e][0] = (uint8_t)(q - 1);
-        pl.cuts[e][1] = (uint8_t)jt;
-        if (q > 2) { // slices of the first walked position b0 in [q-1, jt), each about `cap` subsets per lane
-            u64 cap = std::max<u64>(cap0, (p->binom[jt][q] + TP_SPLIT_MAX_PIECES - 1) / TP_SPLIT_MAX_PIECES);
-            uint8_t desc[TP_SPLIT_MAX_PIECES + 1];
-            int nd = 0;
-            desc[nd++] = (uint8_t)jt;
-            u64 acc = 0;
-            for (int b0 = jt - 1; b0 >= q - 1; b0--) {
-                const u64 w = p->binom[b0][q - 1];
-                if (acc > 0 && acc + w > cap && nd < TP_SPLIT_MAX_PIECES) {
-                    desc[nd++] = (uint8_t)(b0 + 1);
-                    acc = 0;
-                }
-                acc += w;
-            }
-            desc[nd] = (uint8_t)(q - 1);
-            np = nd;
-            for (int i = 0; i <= nd; i++) pl.cuts[e][i] = desc[nd - i]; // ascending
-        }
+        int np = 1; // slices of the first walked position, each about `cap0` subsets per lane
+        if (q > 2) np = (int)std::min<u64>(std::max<u64>((p->binom[jt][q] + cap0 - 1) / cap0, 1), TP_SPLIT_MAX_PIECES);
         pl.item_base[e] = (uint32_t)items;
         pl.n_chunks[e] = (uint32_t)chunks;
         pl.n_pieces[e] = (uint8_t)np;
@@ -413,8 +394,11 @@ u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
         const int jt = pl.jt_hi - e;
         const u64 na = p->binom[n - 1 - jt][pl.p - 1];
         for (int piece = 0; piece < pl.n_pieces[e]; piece++) {
+            auto Cb = [&](int a, int b) -> u64 { return p->binom[a][b]; };
+            const int np = pl.n_pieces[e];
             const u64 per_lane = pl.q == 2 ? p->binom[jt][2]
-                                           : p->binom[pl.cuts[e][piece + 1]][pl.q] - p->binom[pl.cuts[e][piece]][pl.q];
+                                           : p->binom[tp_split_cut(Cb, jt, pl.q, np, piece + 1)][pl.q] -
+                                                 p->binom[tp_split_cut(Cb, jt, pl.q, np, piece)][pl.q];
             for (u64 ac = 0; ac < pl.n_chunks[e]; ac++) {
                 const u64 item = pl.item_base[e] + (u64)piece * pl.n_chunks[e] + ac;
                 if (item % (unsigned)cnt != (unsigned)idx) continue;

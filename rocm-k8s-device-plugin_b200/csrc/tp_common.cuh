@@ -119,7 +119,7 @@ struct TpBatch { // count == 0: single-request mode (all blocks share request 0,
 #define TP_BIG2 0x30003000u
 #define TP_SPLIT_WARPS 8
 #define TP_SPLIT_THREADS (TP_SPLIT_WARPS * 32)
-#define TP_SPLIT_MAX_PIECES 16
+#define TP_SPLIT_MAX_PIECES 64
 #define TP_SPLIT_MAX_P 12
 #define TP_SPLIT_MAX_D 4
 #define TP_SPLIT_SCORE_LIMIT 12000 /* every partial sum must stay below TP_BIG */
@@ -133,8 +133,24 @@ struct TpPlan {
     int32_t min_w;        // smallest weight between two free devices
     uint32_t item_base[TP_MAX_N]; // entry e <-> pivot jt_hi - e
     uint32_t n_chunks[TP_MAX_N];  // chunks of 32 A's
-    uint8_t n_pieces[TP_MAX_N];
-    uint8_t cuts[TP_MAX_N][TP_SPLIT_MAX_PIECES + 1]; // first-B'' position slices [cuts[i], cuts[i+1])
+    uint8_t n_pieces[TP_MAX_N];   // slices of the first walked position, see tp_split_cut
 };
+
+// Slice i of np of the first walked position b0 in [q-1, jt): boundaries put about the same number
+// of subsets (C(b,q) counts those with b0 < b) in every slice; a slice can be empty, since one
+// b0 value is the finest grain.  Used by the kernel (item -> slice) and by the host (counting).
+template <class BinomFn>
+__host__ __device__ inline int tp_split_cut(BinomFn C, int jt, int q, int np, int i) {
+    if (i <= 0) return q - 1;
+    if (i >= np) return jt;
+    const unsigned long long target = C(jt, q) * (unsigned long long)i / (unsigned long long)np;
+    int lo = q - 1, hi = jt; // smallest b with C(b,q) >= target
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (C(mid, q) >= target) hi = mid;
+        else lo = mid + 1;
+    }
+    return lo;
+}
 
 

@@ -325,9 +325,11 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
 
     // the plan's per-pivot tables, block-shared (item -> pivot lookups happen once per item)
     __shared__ uint32_t s_item_base[TP_MAX_N], s_chunks[TP_MAX_N];
+    __shared__ uint8_t s_pieces[TP_MAX_N];
     for (int i = threadIdx.x; i < plan->n_entries; i += blockDim.x) {
         s_item_base[i] = plan->item_base[i];
         s_chunks[i] = plan->n_chunks[i];
+        s_pieces[i] = plan->n_pieces[i];
     }
     __syncthreads();
     TpSplitShared sh{wp, wm, n, k, p, q, rq->dbits, rsp, plan->min_w};
@@ -359,7 +361,13 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
         const unsigned nchunks = s_chunks[e];
         const int piece = (int)(local / nchunks);
         const unsigned ac = local - (unsigned)piece * nchunks;
-        const int b0_lo = plan->cuts[e][piece], b0_hi = plan->cuts[e][piece + 1];
+        int b0_lo = q - 1, b0_hi = jt;
+        if (D > 0) {
+            const int np = s_pieces[e];
+            b0_lo = tp_split_cut(C, jt, q, np, piece);
+            b0_hi = tp_split_cut(C, jt, q, np, piece + 1);
+            if (b0_lo >= b0_hi) continue; // empty slice (one b0 value is the finest grain)
+        }
 
         // ---- this lane's A: rank -> p-1 offsets above the pivot, colexicographic unrank --------
         // (largest first; the smallest offset varies fastest, so neighbouring lanes read
