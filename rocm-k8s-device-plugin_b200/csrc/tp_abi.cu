@@ -57,6 +57,7 @@ struct Prep {
     int kernel = TP_KERNEL_LEX;
     bool family_only = false; // not enumerable and not within the FAMILY kernel's limits either
     u64 family_masks = 0;     // kernel FAMILY: 2^groups bitmasks to visit
+    int shards = 1;           // how many shards the search will be split into (sizes the SPLIT items)
 };
 
 } // namespace
@@ -216,10 +217,12 @@ bool build_plan(const tp_policy *p, Prep &out) {
     pl.jt_hi = n - pp;
     pl.n_entries = n - pp - q + 1;
     pl.min_w = min_w;
-    // Slice so that the longest item (one warp, serial) is a few percent of the whole search,
-    // while one item stays worth >= 2K subsets per lane: the per-item set-up (unrank, lane vector)
-    // is latency-bound and measurably costs throughput when items get small (sweep in DESIGN.md).
-    u64 cap0 = std::min<u64>(std::max<u64>(2048, rq.total / 100000), 65536);
+    // Slice so that the longest item (one warp, serial: ~2.6 ns per subset and lane) stays a few
+    // percent of what one GPU has to do, while an item is worth >= 2K subsets per lane: the
+    // per-item set-up (unrank, lane vector) is latency-bound and costs throughput when items get
+    // small (measured sweep on C4: 3.12 ms at 1K, 2.86 ms at 64K; at 8 shards 64K items leave a
+    // 0.17 ms tail on a 0.37 ms shard).
+    u64 cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (400000ull * (u64)std::max(out.shards, 1))), 65536);
     if (const char *env = getenv("TP_SPLIT_CAP")) cap0 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
     u64 items = 0;
     for (int e = 0; e < pl.n_entries; e++) {
@@ -242,7 +245,8 @@ bool build_plan(const tp_policy *p, Prep &out) {
 // The nine ordered checks and two short-circuits of Allocate (besteffort_policy.go:90-124),
 // then filterPartitions (device.go:310-351) as canonical order + group tables.
 void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
-             Prep &out) {
+             Prep &out, int shards = 1) {
+    out.shards = shards;
     out.status = 0;
     out.shortcut = 0;
     out.n_req = n_req;
@@ -831,7 +835,7 @@ int tp_search_resident(tp_policy *p, const int32_t *avail, int32_t n_avail, cons
         return TP_ERR_BAD_ARGUMENT;
     if (info) memset(info, 0, sizeof *info);
     Prep pr;
-    prepare(p, avail, n_avail, req, n_req, size, pr);
+    prepare(p, avail, n_avail, req, n_req, size, pr, shard_count);
     if (pr.status) return pr.status;
     if (pr.shortcut) return 1;
     if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
@@ -854,7 +858,7 @@ int tp_search_shard(tp_policy *p, const int32_t *avail, int32_t n_avail, const i
     if (!p || !key || shard_count <= 0 || shard_index < 0 || shard_index >= shard_count) return TP_ERR_BAD_ARGUMENT;
     if (info) memset(info, 0, sizeof *info);
     Prep pr;
-    prepare(p, avail, n_avail, req, n_req, size, pr);
+    prepare(p, avail, n_avail, req, n_req, size, pr, shard_count);
     if (pr.status) return pr.status;
     if (pr.shortcut) return 1;
     if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
@@ -893,7 +897,7 @@ int tp_prepare(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_
     *out = nullptr;
     tp_prepared *q = new (std::nothrow) tp_prepared();
     if (!q) return TP_ERR_BAD_ARGUMENT;
-    prepare(p, avail, n_avail, req, n_req, size, q->pr);
+    prepare(p, avail, n_avail, req, n_req, size, q->pr, shard_count);
     int rc = q->pr.status ? q->pr.status : q->pr.shortcut ? 1 : q->pr.family_only ? TP_ERR_TOO_LARGE
              : p->host_only ? TP_ERR_CUDA : 0;
     if (rc) {
