@@ -350,7 +350,28 @@ def latency_leg(tp, dev):
             t = time.perf_counter()
             ref.Allocate(ids, [], size)
             cpu.append((time.perf_counter() - t) * 1e6)
+        # 8 concurrent callers on one policy (one goroutine per RPC in the reference's gRPC server)
+        import threading
+        conc = [[] for _ in range(8)]
+
+        def caller(slot):
+            for _ in range(500):
+                t0 = time.perf_counter()
+                tp.allocate_indices(pol, av, [], size)
+                conc[slot].append((time.perf_counter() - t0) * 1e6)
+
+        threads = [threading.Thread(target=caller, args=(s,)) for s in range(8)]
+        t0 = time.perf_counter()
+        for th in threads:
+            th.start()
+        for th in threads:
+            th.join()
+        conc_s = time.perf_counter() - t0
+        conc_all = [x for c in conc for x in c]
         out[name] = {"subsets": info["subsets_total"], "c_abi_p50_us": percentile(abi, 50),
+                     "c_abi_mean_us": sum(abi) / len(abi),
+                     "concurrent8_p50_us": percentile(conc_all, 50), "concurrent8_p99_us": percentile(conc_all, 99),
+                     "concurrent8_calls_per_s": len(conc_all) / conc_s,
                      "c_abi_p99_us": percentile(abi, 99), "policy_p50_us": percentile(host, 50),
                      "policy_p99_us": percentile(host, 99), "kernel_us": info["kernel_ms"] * 1e3,
                      "cpu_reference_bfs_p50_us": percentile(cpu, 50),
