@@ -81,6 +81,21 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
+def ncu_dram_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the search kernel, from the
+    committed `ncu --set full` summary of this round (profiles/); None when there is none."""
+    name = {1: "r1_lex_ncu_full.txt", 2: "r1_split3_c4_ncu_full.txt"}.get(kernel)
+    path = os.path.join(ROOT, "profiles", name) if name else None
+    if not path or not os.path.exists(path):
+        return None
+    total, unit_scale = 0.0, {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for line in open(path):
+        parts = line.split()
+        if len(parts) >= 4 and parts[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and parts[1] == "=":
+            total += float(parts[2]) * unit_scale.get(parts[3], 1.0)
+    return total
+
+
 def percentile(xs, p):
     xs = sorted(xs)
     return xs[min(len(xs) - 1, int(p / 100.0 * len(xs)))]
@@ -281,7 +296,7 @@ def main():
             peak_src = "IADD3 microbenchmark in this run (tp_measure_int_peak variant 0)"
         achieved = rate * ops_per_subset / 1e12
         roofline = {"bound": "int-alu", "achieved": achieved, "peak": peak_tops, "unit": "Tops/s",
-                    "frac": achieved / peak_tops, "traffic": None, "ops": unit_note,
+                    "frac": achieved / peak_tops, "traffic": ncu_dram_traffic(info["kernel"]), "ops": unit_note,
                     "peak_source": peak_src + "; MEASURED_PEAKS.json has no integer figure",
                     "peak_iadd3_tops": peak_iadd / 1e3, "peak_viaddmnmx_u16x2_glane_instr": peak_addmin,
                     "ops_per_subset": ops_per_subset, "kernel": kname, "kernel_ms": k_ms,
@@ -290,7 +305,8 @@ def main():
                     "hbm_bytes_per_launch_algorithmic": h2d + d2h}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+                "scaling": "strong", "vs_baseline": None,
+                "dtype": "u16" if info["kernel"] == tp.KERNEL_SPLIT else "int32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "sharding": f"rank-range x{world}, one NCCL min all-reduce/step"
                            if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
                            "kernel": {1: "lex", 2: "split"}.get(info["kernel"], str(info["kernel"]))},
