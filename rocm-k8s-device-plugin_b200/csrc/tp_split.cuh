@@ -160,6 +160,122 @@ __device__ __forceinline__ void tp_split_make_p(unsigned (&P)[M / 2], const uint
     }
 }
 
+// ---- two leaves at once -----------------------------------------------------------------------
+// Consecutive leaf positions b and b-1 of one lane share everything except the masked row that
+// enters P, so they are scored together: one set of row loads, address arithmetic and dispatch
+// feeds two independent VIADDMNMX chains (Pa for b, Pb for b-1).  Row jx = b-1 is not a pair of
+// the second leaf and excludes itself: Pb carries TP_BIG at every position >= b-1.  Limited to
+// positions < TP_SPLIT_DUAL_M so that both vectors fit in registers for every M.
+#define TP_SPLIT_DUAL_M 64
+
+template <int M, int JX>
+__device__ __forceinline__ void tp_split_row2(const unsigned (&Pa)[M / 2], const unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+                                              const uint4 *__restrict__ wm4, unsigned &runa, unsigned &runb,
+                                              const uint4 &cur, uint4 &nxt) {
+    constexpr int NFULL = JX / 8, REM = JX % 8;
+    if constexpr (JX > 1) nxt = wm4[(JX - 1) * TpSplitCfg<M>::RS4];
+    constexpr unsigned SEL = (JX & 1) ? 0x3232 : 0x1010;
+    const unsigned pxa = __byte_perm(Pa[JX / 2], 0, SEL), pxb = __byte_perm(Pb[JX / 2], 0, SEL);
+    unsigned acca = TP_BIG2 + TP_BIG2, accb = TP_BIG2 + TP_BIG2;
+#define TP_ROW2_OP(r, w)                          \
+    do {                                          \
+        acca = __viaddmin_u16x2(Pa[r], (w), acca); \
+        accb = __viaddmin_u16x2(Pb[r], (w), accb); \
+    } while (0)
+    if constexpr (NFULL >= 1) {
+        TP_ROW2_OP(0, cur.x);
+        TP_ROW2_OP(1, cur.y);
+        TP_ROW2_OP(2, cur.z);
+        TP_ROW2_OP(3, cur.w);
+#pragma unroll
+        for (int c = 1; c < NFULL; c++) {
+            const uint4 r = wm4[JX * TpSplitCfg<M>::RS4 + c];
+            TP_ROW2_OP(4 * c + 0, r.x);
+            TP_ROW2_OP(4 * c + 1, r.y);
+            TP_ROW2_OP(4 * c + 2, r.z);
+            TP_ROW2_OP(4 * c + 3, r.w);
+        }
+        if constexpr (REM > 4) {
+            const uint4 r = wm4[JX * TpSplitCfg<M>::RS4 + NFULL];
+            TP_ROW2_OP(4 * NFULL + 0, r.x);
+            TP_ROW2_OP(4 * NFULL + 1, r.y);
+            TP_ROW2_OP(4 * NFULL + 2, r.z);
+            if constexpr (REM > 6) TP_ROW2_OP(4 * NFULL + 3, r.w);
+        } else if constexpr (REM > 0) {
+            const uint2 r = ((const uint2 *)wm4)[(JX * TpSplitCfg<M>::RS4 + NFULL) * 2];
+            TP_ROW2_OP(4 * NFULL + 0, r.x);
+            if constexpr (REM > 2) TP_ROW2_OP(4 * NFULL + 1, r.y);
+        }
+    } else {
+        TP_ROW2_OP(0, cur.x);
+        if constexpr (REM > 2) TP_ROW2_OP(1, cur.y);
+        if constexpr (REM > 4) TP_ROW2_OP(2, cur.z);
+        if constexpr (REM > 6) TP_ROW2_OP(3, cur.w);
+    }
+#undef TP_ROW2_OP
+    runa = __viaddmin_u16x2(acca, pxa, runa);
+    runb = __viaddmin_u16x2(accb, pxb, runb);
+}
+
+#define TP_ROW2_CASE(J)                                                                            \
+    case J:                                                                                        \
+        if constexpr ((J) < TP_SPLIT_DUAL_M && (J) >= 1) {                                         \
+            if constexpr ((J) & 1) tp_split_row2<M, (J)>(Pa, Pb, wm4, runa, runb, buf_odd, buf_even); \
+            else tp_split_row2<M, (J)>(Pa, Pb, wm4, runa, runb, buf_even, buf_odd);                  \
+        }                                                                                          \
+        [[fallthrough]];
+#define TP_ROW2_CASE8(B)                                                                                \
+    TP_ROW2_CASE(B + 7) TP_ROW2_CASE(B + 6) TP_ROW2_CASE(B + 5) TP_ROW2_CASE(B + 4) TP_ROW2_CASE(B + 3) \
+    TP_ROW2_CASE(B + 2) TP_ROW2_CASE(B + 1) TP_ROW2_CASE(B + 0)
+
+template <int M>
+__device__ __forceinline__ void tp_split_pairs2(const unsigned (&Pa)[M / 2], const unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+                                                const uint4 *__restrict__ wm4, int start, unsigned &runa,
+                                                unsigned &runb) {
+    runa = TP_BIG2 + TP_BIG2;
+    runb = TP_BIG2 + TP_BIG2;
+    uint4 buf_even = wm4[start * TpSplitCfg<M>::RS4], buf_odd = buf_even;
+    switch (start) {
+        TP_ROW2_CASE8(56) TP_ROW2_CASE8(48) TP_ROW2_CASE8(40) TP_ROW2_CASE8(32) TP_ROW2_CASE8(24) TP_ROW2_CASE8(16)
+        TP_ROW2_CASE8(8) TP_ROW2_CASE8(0)
+    default: break;
+    }
+}
+
+template <int M, int C>
+__device__ __forceinline__ void tp_split_p2_chunk(unsigned (&Pa)[M / 2], unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+                                                  const uint4 *__restrict__ v4, const uint4 *__restrict__ t4,
+                                                  const uint4 *__restrict__ wa4, const uint4 *__restrict__ wb4) {
+    if constexpr (C < TP_SPLIT_DUAL_M / 8) {
+        const uint4 v = v4[C * 32];
+        const uint4 t = t4[C];
+        const uint4 a = wa4[C], b = wb4[C];
+        const unsigned x = v.x + t.x, y = v.y + t.y, z = v.z + t.z, w = v.w + t.w;
+        Pa[4 * C + 0] = x + a.x;
+        Pa[4 * C + 1] = y + a.y;
+        Pa[4 * C + 2] = z + a.z;
+        Pa[4 * C + 3] = w + a.w;
+        Pb[4 * C + 0] = x + b.x;
+        Pb[4 * C + 1] = y + b.y;
+        Pb[4 * C + 2] = z + b.z;
+        Pb[4 * C + 3] = w + b.w;
+    }
+}
+#define TP_P2_CASE(C)                                      \
+    case (C) + 1:                                          \
+        tp_split_p2_chunk<M, (C)>(Pa, Pb, v4, t4, wa4, wb4); \
+        [[fallthrough]];
+template <int M>
+__device__ __forceinline__ void tp_split_make_p2(unsigned (&Pa)[M / 2], unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+                                                 const uint4 *__restrict__ v4, const uint4 *__restrict__ t4,
+                                                 const uint4 *__restrict__ wa4, const uint4 *__restrict__ wb4,
+                                                 int limit) {
+    switch ((limit + 7) >> 3) {
+        TP_P2_CASE(7) TP_P2_CASE(6) TP_P2_CASE(5) TP_P2_CASE(4) TP_P2_CASE(3) TP_P2_CASE(2) TP_P2_CASE(1) TP_P2_CASE(0)
+    default: break;
+    }
+}
+
 struct TpSplitWarp { // per-warp state (uniform unless noted)
     uint16_t *tstack;   // [D+1][M] level vectors
     uint32_t *va;       // [M/8][32][4] lane-private V, packed pairs, 16 bytes per lane per chunk
@@ -251,7 +367,26 @@ struct TpSplitWalk {
             const uint4 *wm4 = (const uint4 *)tp_split_smem;
             const uint4 *v4 = (const uint4 *)w.va + w.lane;
             const int room = *(volatile int *)s_bound - lb - sb + 1; // > score of (b, pair) <=> no candidate
-            for (int b = hi - 1; b >= lo; --b) {
+            unsigned Pb[TP_SPLIT_DUAL_M / 2];
+            int b = hi - 1;
+            while (b >= lo) {
+                if (b <= TP_SPLIT_DUAL_M && b - 1 >= lo) {
+                    // leaves b and b-1 together (P doubles as the first leaf's vector)
+                    tp_split_make_p2<M>(P, Pb, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS),
+                                        (const uint4 *)(sh.wm + (b - 1) * Cfg::RS), b);
+                    unsigned runa, runb;
+                    tp_split_pairs2<M>(P, Pb, wm4, b - 1, runa, runb);
+                    const int va_a = tp_split_va_get(w.va, w.lane, b), va_b = tp_split_va_get(w.va, w.lane, b - 1);
+                    const int ta = tl[b], tb = tl[b - 1];
+                    const unsigned thra = (unsigned)min(max(room - va_a - ta, 0), 0xFFFF) * 0x10001u;
+                    const unsigned thrb = (unsigned)min(max(room - va_b - tb, 0), 0xFFFF) * 0x10001u;
+                    if (__vminu2(runa, thra) != thra && w.active)
+                        tp_split_slow<M>(sh, s, w, D, b, b, lb + va_a + sb + ta, s_bound, best);
+                    if (__vminu2(runb, thrb) != thrb && w.active)
+                        tp_split_slow<M>(sh, s, w, D, b - 1, b - 1, lb + va_b + sb + tb, s_bound, best);
+                    b -= 2;
+                    continue;
+                }
                 tp_split_make_p<M, true>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS), b);
                 const unsigned run = tp_split_pairs<M>(P, wm4, b - 1);
                 const int vab = tp_split_va_get(w.va, w.lane, b);
@@ -259,6 +394,7 @@ struct TpSplitWalk {
                 const unsigned thr2 = (unsigned)thr * 0x10001u;
                 if (__vminu2(run, thr2) != thr2 && w.active)
                     tp_split_slow<M>(sh, s, w, D, b, b, lb + vab + sb + tl[b], s_bound, best);
+                --b;
             }
         }
     }
