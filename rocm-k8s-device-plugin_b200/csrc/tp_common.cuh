@@ -117,6 +117,7 @@ struct TpBatch { // count == 0: single-request mode (all blocks share request 0,
 // ---- kernel SPLIT (tp_split.cuh): constants and the host-built work plan ----------------------
 #define TP_BIG 0x3000u
 #define TP_BIG2 0x30003000u
+#define TP_SPLIT_PREGS 64 /* lane registers holding packed P values: 128 positions, or 2 x 64 for two leaves */
 #define TP_SPLIT_WARPS 8
 #define TP_SPLIT_THREADS (TP_SPLIT_WARPS * 32)
 #define TP_SPLIT_MAX_PIECES 64

@@ -58,7 +58,7 @@ struct TpSplitCfg {
 // this row in turn starts the load of row JX-1 into `nxt`, so the shared-memory latency of the
 // short rows (where the leaves spend their time) overlaps the arithmetic.
 template <int M, int JX>
-__device__ __forceinline__ void tp_split_row(const unsigned (&P)[M / 2], const uint4 *__restrict__ wm4,
+__device__ __forceinline__ void tp_split_row(const unsigned (&P)[TP_SPLIT_PREGS], const uint4 *__restrict__ wm4,
                                              unsigned &run, const uint4 &cur, uint4 &nxt) {
     constexpr int NFULL = JX / 8, REM = JX % 8;
     if constexpr (JX > 1) nxt = wm4[(JX - 1) * TpSplitCfg<M>::RS4];
@@ -110,7 +110,7 @@ __device__ __forceinline__ void tp_split_row(const unsigned (&P)[M / 2], const u
 
 // min over all pairs jx > jy with jx <= start of P[jx] + P[jy] + W[jx][jy], packed per half.
 template <int M>
-__device__ __forceinline__ unsigned tp_split_pairs(const unsigned (&P)[M / 2], const uint4 *__restrict__ wm4,
+__device__ __forceinline__ unsigned tp_split_pairs(const unsigned (&P)[TP_SPLIT_PREGS], const uint4 *__restrict__ wm4,
                                                    int start) {
     unsigned run = TP_BIG2 + TP_BIG2;
     uint4 buf_even = wm4[start * TpSplitCfg<M>::RS4], buf_odd = buf_even; // first chunk of the entry row
@@ -126,7 +126,7 @@ __device__ __forceinline__ unsigned tp_split_pairs(const unsigned (&P)[M / 2], c
 // P = V + T (+ masked row of the leaf position) for the chunks that hold a position < limit:
 // entered at the highest such chunk, falling through to chunk 0.
 template <int M, bool HAS_ROW, int C>
-__device__ __forceinline__ void tp_split_p_chunk(unsigned (&P)[M / 2], const uint4 *__restrict__ v4,
+__device__ __forceinline__ void tp_split_p_chunk(unsigned (&P)[TP_SPLIT_PREGS], const uint4 *__restrict__ v4,
                                                  const uint4 *__restrict__ t4, const uint4 *__restrict__ wb4) {
     if constexpr (C < M / 8) {
         const uint4 v = v4[C * 32]; // lane-private: [chunk][lane]
@@ -150,7 +150,7 @@ __device__ __forceinline__ void tp_split_p_chunk(unsigned (&P)[M / 2], const uin
         tp_split_p_chunk<M, HAS_ROW, (C)>(P, v4, t4, wb4); \
         [[fallthrough]];
 template <int M, bool HAS_ROW>
-__device__ __forceinline__ void tp_split_make_p(unsigned (&P)[M / 2], const uint4 *__restrict__ v4,
+__device__ __forceinline__ void tp_split_make_p(unsigned (&P)[TP_SPLIT_PREGS], const uint4 *__restrict__ v4,
                                                 const uint4 *__restrict__ t4, const uint4 *__restrict__ wb4,
                                                 int limit) {
     switch ((limit + 7) >> 3) { // number of chunks
@@ -167,20 +167,21 @@ __device__ __forceinline__ void tp_split_make_p(unsigned (&P)[M / 2], const uint
 // the second leaf and excludes itself: Pb carries TP_BIG at every position >= b-1.  Limited to
 // positions < TP_SPLIT_DUAL_M so that both vectors fit in registers for every M.
 #define TP_SPLIT_DUAL_M 64
+#define TP_SPLIT_PB (TP_SPLIT_DUAL_M / 2) /* the second leaf's vector lives in the upper half of the register array */
 
 template <int M, int JX>
-__device__ __forceinline__ void tp_split_row2(const unsigned (&Pa)[M / 2], const unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+__device__ __forceinline__ void tp_split_row2(const unsigned (&Pa)[TP_SPLIT_PREGS],
                                               const uint4 *__restrict__ wm4, unsigned &runa, unsigned &runb,
                                               const uint4 &cur, uint4 &nxt) {
     constexpr int NFULL = JX / 8, REM = JX % 8;
     if constexpr (JX > 1) nxt = wm4[(JX - 1) * TpSplitCfg<M>::RS4];
     constexpr unsigned SEL = (JX & 1) ? 0x3232 : 0x1010;
-    const unsigned pxa = __byte_perm(Pa[JX / 2], 0, SEL), pxb = __byte_perm(Pb[JX / 2], 0, SEL);
+    const unsigned pxa = __byte_perm(Pa[JX / 2], 0, SEL), pxb = __byte_perm(Pa[TP_SPLIT_PB + JX / 2], 0, SEL);
     unsigned acca = TP_BIG2 + TP_BIG2, accb = TP_BIG2 + TP_BIG2;
 #define TP_ROW2_OP(r, w)                          \
     do {                                          \
         acca = __viaddmin_u16x2(Pa[r], (w), acca); \
-        accb = __viaddmin_u16x2(Pb[r], (w), accb); \
+        accb = __viaddmin_u16x2(Pa[TP_SPLIT_PB + r], (w), accb); \
     } while (0)
     if constexpr (NFULL >= 1) {
         TP_ROW2_OP(0, cur.x);
@@ -220,8 +221,8 @@ __device__ __forceinline__ void tp_split_row2(const unsigned (&Pa)[M / 2], const
 #define TP_ROW2_CASE(J)                                                                            \
     case J:                                                                                        \
         if constexpr ((J) < TP_SPLIT_DUAL_M && (J) >= 1) {                                         \
-            if constexpr ((J) & 1) tp_split_row2<M, (J)>(Pa, Pb, wm4, runa, runb, buf_odd, buf_even); \
-            else tp_split_row2<M, (J)>(Pa, Pb, wm4, runa, runb, buf_even, buf_odd);                  \
+            if constexpr ((J) & 1) tp_split_row2<M, (J)>(Pa, wm4, runa, runb, buf_odd, buf_even); \
+            else tp_split_row2<M, (J)>(Pa, wm4, runa, runb, buf_even, buf_odd);                  \
         }                                                                                          \
         [[fallthrough]];
 #define TP_ROW2_CASE8(B)                                                                                \
@@ -229,7 +230,7 @@ __device__ __forceinline__ void tp_split_row2(const unsigned (&Pa)[M / 2], const
     TP_ROW2_CASE(B + 2) TP_ROW2_CASE(B + 1) TP_ROW2_CASE(B + 0)
 
 template <int M>
-__device__ __forceinline__ void tp_split_pairs2(const unsigned (&Pa)[M / 2], const unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+__device__ __forceinline__ void tp_split_pairs2(const unsigned (&Pa)[TP_SPLIT_PREGS],
                                                 const uint4 *__restrict__ wm4, int start, unsigned &runa,
                                                 unsigned &runb) {
     runa = TP_BIG2 + TP_BIG2;
@@ -243,7 +244,7 @@ __device__ __forceinline__ void tp_split_pairs2(const unsigned (&Pa)[M / 2], con
 }
 
 template <int M, int C>
-__device__ __forceinline__ void tp_split_p2_chunk(unsigned (&Pa)[M / 2], unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+__device__ __forceinline__ void tp_split_p2_chunk(unsigned (&Pa)[TP_SPLIT_PREGS],
                                                   const uint4 *__restrict__ v4, const uint4 *__restrict__ t4,
                                                   const uint4 *__restrict__ wa4, const uint4 *__restrict__ wb4) {
     if constexpr (C < TP_SPLIT_DUAL_M / 8) {
@@ -255,18 +256,18 @@ __device__ __forceinline__ void tp_split_p2_chunk(unsigned (&Pa)[M / 2], unsigne
         Pa[4 * C + 1] = y + a.y;
         Pa[4 * C + 2] = z + a.z;
         Pa[4 * C + 3] = w + a.w;
-        Pb[4 * C + 0] = x + b.x;
-        Pb[4 * C + 1] = y + b.y;
-        Pb[4 * C + 2] = z + b.z;
-        Pb[4 * C + 3] = w + b.w;
+        Pa[TP_SPLIT_PB + 4 * C + 0] = x + b.x;
+        Pa[TP_SPLIT_PB + 4 * C + 1] = y + b.y;
+        Pa[TP_SPLIT_PB + 4 * C + 2] = z + b.z;
+        Pa[TP_SPLIT_PB + 4 * C + 3] = w + b.w;
     }
 }
 #define TP_P2_CASE(C)                                      \
     case (C) + 1:                                          \
-        tp_split_p2_chunk<M, (C)>(Pa, Pb, v4, t4, wa4, wb4); \
+        tp_split_p2_chunk<M, (C)>(Pa, v4, t4, wa4, wb4);   \
         [[fallthrough]];
 template <int M>
-__device__ __forceinline__ void tp_split_make_p2(unsigned (&Pa)[M / 2], unsigned (&Pb)[TP_SPLIT_DUAL_M / 2],
+__device__ __forceinline__ void tp_split_make_p2(unsigned (&Pa)[TP_SPLIT_PREGS],
                                                  const uint4 *__restrict__ v4, const uint4 *__restrict__ t4,
                                                  const uint4 *__restrict__ wa4, const uint4 *__restrict__ wb4,
                                                  int limit) {
@@ -345,7 +346,7 @@ __device__ __noinline__ void tp_split_slow(const TpSplitShared &sh, const TpSmem
 template <int M, int D, int L>
 struct TpSplitWalk {
     static __device__ __forceinline__ void run(const TpSplitShared &sh, const TpSmem &s, TpSplitWarp &w,
-                                               unsigned (&P)[M / 2], int hi, int lo, int lb, int sb,
+                                               unsigned (&P)[TP_SPLIT_PREGS], int hi, int lo, int lb, int sb,
                                                int *s_bound, TpKey &best) {
         using Cfg = TpSplitCfg<M>;
         const uint16_t *tl = w.tstack + L * M;
@@ -367,33 +368,35 @@ struct TpSplitWalk {
             const uint4 *wm4 = (const uint4 *)tp_split_smem;
             const uint4 *v4 = (const uint4 *)w.va + w.lane;
             const int room = *(volatile int *)s_bound - lb - sb + 1; // > score of (b, pair) <=> no candidate
-            unsigned Pb[TP_SPLIT_DUAL_M / 2];
+            unsigned Pa[TP_SPLIT_PB + TP_SPLIT_DUAL_M / 2];
             int b = hi - 1;
             while (b >= lo) {
-                if (b <= TP_SPLIT_DUAL_M && b - 1 >= lo) {
+                if (b <= TP_SPLIT_DUAL_M) { // (a leftover single leaf drags a dummy partner b-1 >= 1 along)
                     // leaves b and b-1 together (P doubles as the first leaf's vector)
-                    tp_split_make_p2<M>(P, Pb, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS),
+                    tp_split_make_p2<M>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS),
                                         (const uint4 *)(sh.wm + (b - 1) * Cfg::RS), b);
                     unsigned runa, runb;
-                    tp_split_pairs2<M>(P, Pb, wm4, b - 1, runa, runb);
+                    tp_split_pairs2<M>(P, wm4, b - 1, runa, runb);
                     const int va_a = tp_split_va_get(w.va, w.lane, b), va_b = tp_split_va_get(w.va, w.lane, b - 1);
                     const int ta = tl[b], tb = tl[b - 1];
                     const unsigned thra = (unsigned)min(max(room - va_a - ta, 0), 0xFFFF) * 0x10001u;
                     const unsigned thrb = (unsigned)min(max(room - va_b - tb, 0), 0xFFFF) * 0x10001u;
                     if (__vminu2(runa, thra) != thra && w.active)
                         tp_split_slow<M>(sh, s, w, D, b, b, lb + va_a + sb + ta, s_bound, best);
-                    if (__vminu2(runb, thrb) != thrb && w.active)
+                    if (__vminu2(runb, thrb) != thrb && w.active && b - 1 >= lo)
                         tp_split_slow<M>(sh, s, w, D, b - 1, b - 1, lb + va_b + sb + tb, s_bound, best);
                     b -= 2;
                     continue;
                 }
-                tp_split_make_p<M, true>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS), b);
-                const unsigned run = tp_split_pairs<M>(P, wm4, b - 1);
-                const int vab = tp_split_va_get(w.va, w.lane, b);
-                const int thr = min(max(room - vab - (int)tl[b], 0), 0xFFFF);
-                const unsigned thr2 = (unsigned)thr * 0x10001u;
-                if (__vminu2(run, thr2) != thr2 && w.active)
-                    tp_split_slow<M>(sh, s, w, D, b, b, lb + vab + sb + tl[b], s_bound, best);
+                if constexpr (M > TP_SPLIT_DUAL_M) { // positions above 64: one leaf at a time
+                    tp_split_make_p<M, true>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS), b);
+                    const unsigned run = tp_split_pairs<M>(P, wm4, b - 1);
+                    const int vab = tp_split_va_get(w.va, w.lane, b);
+                    const int thr = min(max(room - vab - (int)tl[b], 0), 0xFFFF);
+                    const unsigned thr2 = (unsigned)thr * 0x10001u;
+                    if (__vminu2(run, thr2) != thr2 && w.active)
+                        tp_split_slow<M>(sh, s, w, D, b, b, lb + vab + sb + tl[b], s_bound, best);
+                }
                 --b;
             }
         }
@@ -575,7 +578,7 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
         else per_lane = C(b0_hi, q) - C(b0_lo, q);
         if (lane == 0) counted += per_lane * (u64)min((u64)32, NA - (u64)ac * 32);
 
-        unsigned P[Cfg::NREG];
+        unsigned P[TP_SPLIT_PREGS];
         if constexpr (D == 0) {
             tp_split_make_p<M, false>(P, (const uint4 *)va + lane, (const uint4 *)tstack, nullptr, jt);
             const unsigned run = tp_split_pairs<M>(P, (const uint4 *)tp_split_smem, jt - 1);
