@@ -201,3 +201,38 @@ def test_family_kernel(pols, name):
             big += 1
     assert big > 10
     fam.close()
+
+
+def test_widest_topology_and_two_word_keys():
+    """128 devices (TP_MAX_DEVICES): the M = 128 instantiations of SPLIT, LEX at full width, and
+    winners whose group sequence spills into key.lo (16 groups = 4-bit digits, k' >= 9)."""
+    devs, pairs = topo.wide_topology()
+    ref = RefPolicy()
+    ref.InitPairs(devs, pairs)
+    pol = tp.BestEffortPolicy(cuda_device=0)
+    pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+    ids = [d.Id for d in devs]
+    gen = topo.SplitMix64(0x128)
+    kernels, wide_keys = set(), 0
+    cases = [(ids, [], 4), (ids, [ids[5]], 5), (ids[3:], [], 5), (ids, [], 2), (ids, [], 3)]
+    # one free device in each of the 16 groups, k' >= 9: the winner touches >= 9 groups, so its 4-bit
+    # digits spill into key.lo.  (The reference's BFS would walk 16!/6! orderings here; the oracle's
+    # exhaustive scorer, shown equal to the BFS in test_oracle_golden.py, answers instead.)
+    singles = [ids[g * 8 + (g % 3)] for g in range(16)]
+    wide_cases = [(singles, [], 10), (singles, [singles[4]], 11), (singles[1:], [], 9)]
+    for _ in range(4):   # wide pools, k' = 4..5: n - p > 96 -> M = 128
+        pool = [i for i in ids if gen.chance(0.9)]
+        cases.append((pool, [], 4 + gen.below(2)))
+    for av, rq, k in cases + wide_cases:
+        exhaustive = (av, rq, k) in wide_cases
+        want = ref.AllocateExhaustive(av, rq, k) if exhaustive else ref.Allocate(av, rq, k)
+        got = pol.Allocate(av, rq, k)
+        assert got == want, (len(av), rq, k)
+        assert pol.last["score"] == ref.last["score"]
+        kernels.add(pol.last["kernel"])
+        wide_keys += pol.last["key"][1] != 0
+        # shards of the same request must min-reduce (two words) to the same winner
+        keys = [pol.SearchShard(av, rq, k, s, 3) for s in range(3)]
+        assert pol.Decode(av, rq, k, min(keys)) == want
+    assert tp.KERNEL_SPLIT in kernels and wide_keys > 0
+    pol.close()

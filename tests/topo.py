@@ -136,3 +136,14 @@ def missing_links_topology(seed=7, frac=0.15):
     """8 groups x 4 with ~15% of the pairs absent from p2pWeights (weight 0)."""
     gen = SplitMix64(seed)
     return synthetic_topology(8, 4, drop=lambda a, b: gen.chance(frac))
+
+
+def wide_topology():
+    """16 groups x 8 = 128 devices (the ABI's maximum), 4 NUMA nodes, XGMI inside pairs of groups, PCIe across."""
+    devs, _ = synthetic_topology(16, 8, numa_count=4)
+    pairs = []
+    for i, a in enumerate(devs):
+        for b in devs[i + 1:]:
+            ty = 11 if int(a.DevId) // 2 == int(b.DevId) // 2 else 2
+            pairs.append((a.NodeId, b.NodeId, pair_weight(a, b, ty)))
+    return devs, pairs
