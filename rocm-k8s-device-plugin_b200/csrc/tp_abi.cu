@@ -7,6 +7,7 @@
 // itself (device.go:353-442 + the argmin) always runs on the GPU; there is no CPU path.
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
@@ -710,6 +711,12 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         }
         return TP_OK;
     }
+    const bool trace = getenv("TP_BATCH_TRACE") != nullptr; // phase timings on stderr (tuning aid)
+    auto now = [] { return std::chrono::steady_clock::now(); };
+    auto ms_since = [&](std::chrono::steady_clock::time_point t0) {
+        return std::chrono::duration<double, std::milli>(now() - t0).count();
+    };
+    const auto t_start = now();
     std::vector<Prep> preps(n_requests);
     {
         const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
@@ -724,6 +731,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         work(0);
         for (std::thread &t : pool) t.join();
     }
+    const double t_prepare = ms_since(t_start);
     std::vector<BatchGroup> groups;
     std::vector<int> singles; // served by tp_allocate after the batch
     size_t n_plans = 0;
@@ -783,6 +791,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
                 b.h_order[n_order++] = e;
             }
         }
+        const double t_stage = ms_since(t_start);
         TP_CUDA(p, cudaMemcpyAsync(b.d_reqs, b.h_reqs, (size_t)n_requests * sizeof(TpReq), cudaMemcpyHostToDevice, b.stream));
         if (plan_at)
             TP_CUDA(p, cudaMemcpyAsync(b.d_plans, b.h_plans, plan_at * sizeof(TpPlan), cudaMemcpyHostToDevice, b.stream));
@@ -802,6 +811,9 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         TP_CUDA(p, cudaMemcpyAsync(b.h_results, b.d_results, (size_t)n_requests * sizeof(TpBatchOut),
                                    cudaMemcpyDeviceToHost, b.stream));
         TP_CUDA(p, cudaStreamSynchronize(b.stream));
+        if (trace)
+            fprintf(stderr, "tp_allocate_batch: %d requests, %zu groups: prepare %.2f ms, stage %.2f ms, gpu %.2f ms\n",
+                    n_requests, groups.size(), t_prepare, t_stage - t_prepare, ms_since(t_start) - t_stage);
         for (const BatchGroup &grp : groups)
             for (int i : grp.members) {
                 const TpKey key = b.h_results[i].key;
