@@ -771,11 +771,25 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
     if (!groups.empty()) {
         std::lock_guard<std::mutex> batch_lock(p->batch.mu);
         DeviceGuard guard(p->cuda_device);
-        int rc = batch_reserve(p, (size_t)n_requests, n_plans);
+        // Heavy requests are cut into shares taken by different blocks (the same item striding as
+        // multi-GPU shards), so that one big search does not become the tail of its group.
+        auto shares_of = [&](int i) -> int {
+            if (preps[i].kernel != TP_KERNEL_SPLIT) return 1;
+            const u64 t = preps[i].rq.total;
+            return t <= (1ull << 24) ? 1 : (int)std::min<u64>(16, (t >> 24) + 1);
+        };
+        size_t n_out = 0;
+        std::vector<int> out_base(n_requests, -1);
+        for (const BatchGroup &grp : groups)
+            for (int i : grp.members) {
+                out_base[i] = (int)n_out;
+                n_out += (size_t)shares_of(i);
+            }
+        int rc = batch_reserve(p, std::max<size_t>((size_t)n_requests, n_out), n_plans);
         if (rc) return rc;
         tp_policy::Batch &b = p->batch;
         size_t n_order = 0, plan_at = 0;
-        std::vector<size_t> first(groups.size());
+        std::vector<size_t> first(groups.size()), n_entries(groups.size());
         for (size_t g = 0; g < groups.size(); g++) {
             BatchGroup &grp = groups[g];
             std::sort(grp.members.begin(), grp.members.end(),
@@ -783,13 +797,16 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
             first[g] = n_order;
             for (int i : grp.members) {
                 b.h_reqs[i] = preps[i].rq;
-                TpBatchEntry e{i, 0};
+                int plan_idx = 0;
                 if (grp.kernel == TP_KERNEL_SPLIT) {
                     b.h_plans[plan_at] = preps[i].plan;
-                    e.plan = (int32_t)plan_at++;
+                    plan_idx = (int)plan_at++;
                 }
-                b.h_order[n_order++] = e;
+                const int S = shares_of(i);
+                for (int sidx = 0; sidx < S; sidx++)
+                    b.h_order[n_order++] = TpBatchEntry{i, plan_idx, out_base[i] + sidx, (int16_t)sidx, (int16_t)S};
             }
+            n_entries[g] = n_order - first[g];
         }
         const double t_stage = ms_since(t_start);
         TP_CUDA(p, cudaMemcpyAsync(b.d_reqs, b.h_reqs, (size_t)n_requests * sizeof(TpReq), cudaMemcpyHostToDevice, b.stream));
@@ -798,7 +815,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         TP_CUDA(p, cudaMemcpyAsync(b.d_order, b.h_order, n_order * sizeof(TpBatchEntry), cudaMemcpyHostToDevice, b.stream));
         for (size_t g = 0; g < groups.size(); g++) {
             const BatchGroup &grp = groups[g];
-            TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + g, (int32_t)grp.members.size(), 0};
+            TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + g, (int32_t)n_entries[g], 0};
             TpLaunchInfo li{};
             if (grp.kernel == TP_KERNEL_SPLIT)
                 TP_CUDA(p, tp_launch_batch_split(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
@@ -808,21 +825,27 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
                                                p->sm_count, b.stream, &li));
             launches += li.launches;
         }
-        TP_CUDA(p, cudaMemcpyAsync(b.h_results, b.d_results, (size_t)n_requests * sizeof(TpBatchOut),
-                                   cudaMemcpyDeviceToHost, b.stream));
+        TP_CUDA(p, cudaMemcpyAsync(b.h_results, b.d_results, n_out * sizeof(TpBatchOut), cudaMemcpyDeviceToHost,
+                                   b.stream));
         TP_CUDA(p, cudaStreamSynchronize(b.stream));
         if (trace)
             fprintf(stderr, "tp_allocate_batch: %d requests, %zu groups: prepare %.2f ms, stage %.2f ms, gpu %.2f ms\n",
                     n_requests, groups.size(), t_prepare, t_stage - t_prepare, ms_since(t_start) - t_stage);
         for (const BatchGroup &grp : groups)
             for (int i : grp.members) {
-                const TpKey key = b.h_results[i].key;
+                TpKey key = b.h_results[out_base[i]].key; // min over the request's shares
+                u64 scored = b.h_results[out_base[i]].scored;
+                for (int sidx = 1; sidx < shares_of(i); sidx++) {
+                    const TpBatchOut &part = b.h_results[out_base[i] + sidx];
+                    if (tp_key_less(part.key, key)) key = part.key;
+                    scored += part.scored;
+                }
                 status[i] = decode(preps[i], key, rqs[i].required, out + (size_t)i * out_stride);
                 if (infos) {
                     tp_result &r = infos[i];
                     r.searched = 1;
                     r.kernel = preps[i].kernel;
-                    r.subsets_scored = b.h_results[i].scored;
+                    r.subsets_scored = scored;
                     r.subsets_total = preps[i].rq.total;
                     r.gpu_launches = launches; // launches of the whole batch (shared by its requests)
                     r.key.hi = key.hi;

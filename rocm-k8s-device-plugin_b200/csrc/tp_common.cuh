@@ -98,8 +98,11 @@ struct TpScratch {
 // Batch mode (tp_allocate_batch): one block per request.  `slot` indexes the batch's request and
 // result arrays, `plan` the (SPLIT-only) plan array.
 struct TpBatchEntry {
-    int32_t slot;
-    int32_t plan;
+    int32_t slot;       // request
+    int32_t plan;       // its plan (SPLIT)
+    int32_t out;        // where in `results` this entry reports
+    int16_t share_idx;  // heavy requests are cut into shares (items share_idx, share_idx + share_cnt, ..)
+    int16_t share_cnt;  // that different blocks take; the host min-reduces the shares
 };
 struct TpBatchOut {
     TpKey key;

@@ -115,13 +115,14 @@ tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
     for (int iter = 0;; iter++) {
         const TpReq *rq = reqs;
         u64 gtid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
-        int slot = 0;
+        int slot = 0, out = 0;
         if (batch.count > 0) {
             __syncthreads(); // everybody is done with the previous request's shared memory
             if (threadIdx.x == 0) s_entry = atomicAdd(batch.grab, 1u);
             __syncthreads();
             if (s_entry >= (unsigned)batch.count) break;
             slot = batch.order[s_entry].slot;
+            out = batch.order[s_entry].out;
             rq = reqs + slot;
             lo = 0;
             hi = rq->total;
@@ -136,8 +137,8 @@ tp_exhaustive_lex(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
         if (batch.count > 0) {
             tp_block_reduce(best, counted);
             if (threadIdx.x == 0) {
-                batch.results[slot].key = best;
-                batch.results[slot].scored = counted;
+                batch.results[out].key = best;
+                batch.results[out].scored = counted;
             }
         } else {
             tp_block_finish(best, counted, sc);

@@ -602,7 +602,7 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
                     TpScratch sc, unsigned *work_counter, TpBatch batch) {
     __shared__ unsigned s_entry, s_items;
     for (int iter = 0;; iter++) {
-        int slot = 0, plan = 0;
+        int slot = 0, plan = 0, out = 0;
         unsigned *wc = work_counter;
         if (batch.count > 0) {
             __syncthreads(); // everybody is done with the previous request's shared memory
@@ -612,8 +612,12 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
             }
             __syncthreads();
             if (s_entry >= (unsigned)batch.count) break;
-            slot = batch.order[s_entry].slot;
-            plan = batch.order[s_entry].plan;
+            const TpBatchEntry en = batch.order[s_entry];
+            slot = en.slot;
+            plan = en.plan;
+            out = en.out;
+            shard_idx = en.share_idx;
+            shard_cnt = en.share_cnt;
             wc = &s_items;
         } else if (iter > 0) {
             break;
@@ -624,8 +628,8 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
         if (batch.count > 0) {
             tp_block_reduce(best, counted);
             if (threadIdx.x == 0) {
-                batch.results[slot].key = best;
-                batch.results[slot].scored = counted;
+                batch.results[out].key = best;
+                batch.results[out].scored = counted;
             }
         } else {
             tp_block_finish(best, counted, sc); // the work counter is re-armed by the launcher's memset
