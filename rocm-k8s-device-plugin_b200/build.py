@@ -15,7 +15,7 @@ ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libtpalloc.so")
-SPLIT_UNITS = [f"csrc/tp_split_m{m}_d{d}.cu" for m in (128, 96, 64) for d in (4, 3, 2, 1, 0)]  # slowest first
+SPLIT_UNITS = [f"csrc/tp_split_m{m}_d{d}.cu" for m in (128, 96, 80, 64) for d in (4, 3, 2, 1, 0)]  # slowest first
 SOURCES = SPLIT_UNITS + ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
 HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_device.cuh", "csrc/tp_split.cuh",
            "host/besteffort_policy.h"]

@@ -751,7 +751,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         key.kernel = pr.kernel;
         if (pr.kernel == TP_KERNEL_SPLIT) {
             const int need = pr.rq.n - pr.plan.p;
-            key.a = pr.plan.p; key.b = pr.plan.q; key.c = need <= 64 ? 64 : need <= 96 ? 96 : 128;
+            key.a = pr.plan.p; key.b = pr.plan.q; key.c = need <= 64 ? 64 : need <= 80 ? 80 : need <= 96 ? 96 : 128;
             n_plans++;
         } else {
             key.a = pr.rq.k; key.b = 0; key.c = 0;

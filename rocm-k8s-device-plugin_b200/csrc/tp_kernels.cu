@@ -429,6 +429,7 @@ static cudaError_t tp_dispatch_split(int D, int need, const uint8_t *d_weight, i
     default: return cudaErrorInvalidValue;                     \
     }
     if (need <= 64) { TP_SPLIT_BY_DEPTH(64) }
+    if (need <= 80) { TP_SPLIT_BY_DEPTH(80) }
     if (need <= 96) { TP_SPLIT_BY_DEPTH(96) }
     if (need <= 128) { TP_SPLIT_BY_DEPTH(128) }
 #undef TP_SPLIT_BY_DEPTH

@@ -40,6 +40,7 @@ cudaError_t tp_launch_batch_lex(const uint8_t *d_weight, int n_devices, const un
     TP_DECLARE_SPLIT_LAUNCHER(M, 0) TP_DECLARE_SPLIT_LAUNCHER(M, 1) TP_DECLARE_SPLIT_LAUNCHER(M, 2)    \
     TP_DECLARE_SPLIT_LAUNCHER(M, 3) TP_DECLARE_SPLIT_LAUNCHER(M, 4)
 TP_DECLARE_SPLIT_LAUNCHERS(64)
+TP_DECLARE_SPLIT_LAUNCHERS(80)
 TP_DECLARE_SPLIT_LAUNCHERS(96)
 TP_DECLARE_SPLIT_LAUNCHERS(128)
 

@@ -1,5 +1,5 @@
 // kernel SPLIT, lane vectors of 128 positions, walk depth 3 (see tp_split.cuh); one translation
-// unit per instantiation so that the 15 of them compile in parallel.
+// unit per instantiation so that all of them compile in parallel.
 #include "tp_split.cuh"
 
 TP_DEFINE_SPLIT_LAUNCHER(128, 3)

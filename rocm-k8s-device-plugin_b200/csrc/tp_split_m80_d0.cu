@@ -1,0 +1,5 @@
+// kernel SPLIT, lane vectors of 80 positions, walk depth 0 (see tp_split.cuh); one translation
+// unit per instantiation so that all of them compile in parallel.
+#include "tp_split.cuh"
+
+TP_DEFINE_SPLIT_LAUNCHER(80, 0)
