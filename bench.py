@@ -286,7 +286,7 @@ def main():
         if info["kernel"] == tp.KERNEL_SPLIT:
             # SPLIT executes one 16-bit add and one 16-bit min per subset (VIADDMNMX.U16x2: two
             # subsets per lane-instruction); the peak is that instruction's measured rate x 4 ops.
-            ops_per_subset, kname, unit_note = 2, "tp_exhaustive_split<96,2>", "16-bit integer add/min ops"
+            ops_per_subset, kname, unit_note = 2, "tp_exhaustive_split<80,2>", "16-bit integer add/min ops"
             peak_tops = peak_addmin * 4 / 1e3
             peak_src = "VIADDMNMX.U16x2 microbenchmark in this run (tp_measure_int_peak variant 3) x 4 ops/lane-instr"
         else:
