@@ -307,7 +307,7 @@ def main():
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None,
                 "dtype": "u16" if info["kernel"] == tp.KERNEL_SPLIT else "int32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "sharding": f"rank-range x{world}, one NCCL min all-reduce/step"
+                "config": {"workload": WORKLOAD, "sharding": f"subset space split x{world} (item stride), one NCCL min all-reduce/step"
                            if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
                            "kernel": {1: "lex", 2: "split"}.get(info["kernel"], str(info["kernel"]))},
                 "clocks": clocks,

@@ -128,8 +128,9 @@ int tp_allocate(tp_policy *p, const int32_t *available, int32_t n_available, con
 int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *requests, int32_t *out,
                       int32_t out_stride, int32_t *status, tp_result *infos);
 
-/* Multi-GPU: score only shard `shard_index` of `shard_count` equal slices of the
- * subset space and return the shard's packed winner; the caller min-reduces keys
+/* Multi-GPU: score only shard `shard_index` of `shard_count` disjoint, equally heavy slices of
+ * the subset space (rank ranges, or a stride of the work-item list) and return the shard's
+ * packed winner; the caller min-reduces keys
  * across shards (one ncclMin all-reduce on key.hi when key.lo is always 0) and
  * decodes the winner with tp_decode.  Requests answered by a short-circuit return
  * 1 and leave key untouched (call tp_allocate for them). */

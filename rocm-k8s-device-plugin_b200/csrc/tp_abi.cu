@@ -469,7 +469,7 @@ int run_search_fast(tp_policy *p, Ctx &c, const Prep &pr, TpKey *key, tp_result 
 // Upload the prepared request, run the search over shard (idx of cnt) `iters` times, fetch the key.
 int run_search(tp_policy *p, Ctx &c, const Prep &pr, int shard_idx, int shard_cnt, int iters, bool upload,
                TpKey *key, tp_result *info, float *total_ms) {
-    if (pr.family_only) return TP_ERR_TOO_LARGE; // Family-only kernel: see tp_family (next milestone)
+    if (pr.family_only) return TP_ERR_TOO_LARGE; // neither enumerable nor within kernel FAMILY's limits
     const TpReq &rq = pr.rq;
     const bool nonempty = shard_nonempty(pr, shard_idx, shard_cnt);
     if (upload) TP_CUDA(p, upload_request(c, pr));
