@@ -223,6 +223,11 @@ def test_widest_topology_and_two_word_keys():
     for _ in range(4):   # wide pools, k' = 4..5: n - p > 96 -> M = 128
         pool = [i for i in ids if gen.chance(0.9)]
         cases.append((pool, [], 4 + gen.below(2)))
+    # deeper walks at the wide lane vectors: (n free, k') -> (M, D)
+    cases.append((ids[:100], [ids[7]], 8))   # 99 free, k' = 7: M = 96,  D = 1
+    cases.append((ids, [], 7))               # 128 free, k' = 7: M = 128, D = 1
+    cases.append((ids[:96], [], 8))          # 96 free,  k' = 8: M = 96,  D = 2
+    cases.append((ids[:84], [], 8))          # 84 free,  k' = 8: M = 80,  D = 2
     for av, rq, k in cases + wide_cases:
         exhaustive = (av, rq, k) in wide_cases
         want = ref.AllocateExhaustive(av, rq, k) if exhaustive else ref.Allocate(av, rq, k)
