@@ -122,6 +122,18 @@ void tp_destroy(tp_policy *p);
 int tp_allocate(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
                 int32_t n_required, int32_t size, int32_t *out, tp_result *info);
 
+/* Advisory mode (off the allocation path; no counterpart in the reference): the minimum of
+ * TotalWeight over ALL subsets of the request, i.e. the same search without the restriction to
+ * the sets the reference's BFS can emit (device.go:375-440).  Same arguments, validation,
+ * short-circuits and return values as tp_allocate; out receives one optimal set (ties: the
+ * first in canonical order; free devices in canonical order, required last) and info->score
+ * its weight, to be compared with tp_allocate's info->score: equal on fully linked topologies,
+ * lower where links are missing and the reference's candidate family misses the optimum.
+ * Limits: (size - n_required) * ceil(log2 free devices) <= 96 and an enumerable subset
+ * count (tp_options.exhaustive_limit), else TP_ERR_TOO_LARGE. */
+int tp_global_optimum(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+                      int32_t n_required, int32_t size, int32_t *out, tp_result *info);
+
 /* The ContainerRequests loop of AMDGPUKFDImpl.GetPreferredAllocation
  * (internal/pkg/amdgpu/amdgpu.go:307-317) as one call.  out is n_requests rows of
  * out_stride int32; status[i] receives what tp_allocate would have returned. */

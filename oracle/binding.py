@@ -78,6 +78,9 @@ def lib() -> C.CDLL:
         L.ref_exhaustive_allocate.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int,
                                               C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_char_p,
                                               C.POINTER(_ExhResult), C.c_int, C.c_ulonglong, C.c_ulonglong]
+        L.ref_exhaustive_global_optimum.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.c_int,
+                                                    C.POINTER(C.c_char_p), C.c_int, C.c_int, C.c_char_p,
+                                                    C.POINTER(_ExhResult), C.c_int]
         for f in ("ref_policy_weight_rows", "ref_policy_group_count", "ref_policy_pair_count",
                   "ref_policy_max_node"):
             getattr(L, f).argtypes = [C.c_void_p]
@@ -153,6 +156,17 @@ class RefPolicy:
         rc = self._check(lib().ref_exhaustive_allocate(self._p, _strs(available), len(available),
                                                        _strs(required), len(required), size, out, C.byref(res),
                                                        threads, rank_lo, rank_hi))
+        self.last = {f: getattr(res, f) for f, _ in _ExhResult._fields_}
+        return [out.raw[i * ID_LEN:(i + 1) * ID_LEN].split(b"\0", 1)[0].decode() for i in range(rc)]
+
+    def GlobalOptimum(self, available, required, size, threads=0):
+        """Minimum of Score over ALL subsets (no Family test); ties: first in canonical order."""
+        required = required or []
+        out = C.create_string_buffer(ID_LEN * max(size, 1))
+        res = _ExhResult()
+        rc = self._check(lib().ref_exhaustive_global_optimum(self._p, _strs(available), len(available),
+                                                             _strs(required), len(required), size, out,
+                                                             C.byref(res), threads))
         self.last = {f: getattr(res, f) for f, _ in _ExhResult._fields_}
         return [out.raw[i * ID_LEN:(i + 1) * ID_LEN].split(b"\0", 1)[0].decode() for i in range(rc)]
 

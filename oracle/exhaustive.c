@@ -233,10 +233,10 @@ static int build_ctx(const ref_policy *p, const int *avail_nodes, int n_avail, c
  * (rank_hi == 0: everything); a partial range is only meaningful for timing.
  * n_threads <= 0 uses all OpenMP threads.
  */
-int ref_exhaustive_allocate(const ref_policy *p, const char *const *avail, int n_avail,
-                            const char *const *req, int n_req, int size, char *out,
-                            ref_exh_result *res, int n_threads, unsigned long long rank_lo,
-                            unsigned long long rank_hi) {
+static int exhaustive_impl(const ref_policy *p, const char *const *avail, int n_avail,
+                           const char *const *req, int n_req, int size, char *out,
+                           ref_exh_result *res, int n_threads, unsigned long long rank_lo,
+                           unsigned long long rank_hi, int unconstrained) {
     if (res) memset(res, 0, sizeof *res);
     if (size <= 0) return REF_ERR_INVALID_SIZE;
     if (n_avail < size) return REF_ERR_INVALID_AVAILABLE;
@@ -273,6 +273,14 @@ int ref_exhaustive_allocate(const ref_policy *p, const char *const *avail, int n
     }
     if (!rc) rc = build_ctx(p, avail_nodes, n_avail, req_nodes, n_req, size, x, canon);
     if (rc) goto done;
+    if (unconstrained) { /* every free device its own group: Family = all subsets */
+        for (int i = 0; i < x->n; i++) {
+            x->group_of[i] = i;
+            x->g_start[i] = i;
+            x->g_size[i] = 1;
+        }
+        x->n_groups = x->n;
+    }
 
     unsigned long long total = x->binom[x->n][x->k];
     if (rank_hi == 0 || rank_hi > total) rank_hi = total;
@@ -370,4 +378,24 @@ done:
     free(canon);
     free(x);
     return rc;
+}
+
+int ref_exhaustive_allocate(const ref_policy *p, const char *const *avail, int n_avail,
+                            const char *const *req, int n_req, int size, char *out,
+                            ref_exh_result *res, int n_threads, unsigned long long rank_lo,
+                            unsigned long long rank_hi) {
+    return exhaustive_impl(p, avail, n_avail, req, n_req, size, out, res, n_threads, rank_lo, rank_hi, 0);
+}
+
+/*
+ * The unconstrained optimum (the advisory mode): the same
+ * enumeration with the Family test dropped, i.e. the minimum of Score over ALL k'-subsets of
+ * the free devices; ties go to the lexicographically first subset in canonical order.  The
+ * reference has no such function: this is the checker of tp_global_optimum, and its score is
+ * what the reference's pick (besteffort_policy.go:133-140) is compared with.
+ */
+int ref_exhaustive_global_optimum(const ref_policy *p, const char *const *avail, int n_avail,
+                                  const char *const *req, int n_req, int size, char *out,
+                                  ref_exh_result *res, int n_threads) {
+    return exhaustive_impl(p, avail, n_avail, req, n_req, size, out, res, n_threads, 0, 0, 1);
 }

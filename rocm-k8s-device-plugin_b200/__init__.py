@@ -110,6 +110,7 @@ def lib() -> C.CDLL:
     L.tp_destroy.restype = None
     req_args = [C.c_void_p, I32P, C.c_int32, I32P, C.c_int32, C.c_int32]
     L.tp_allocate.argtypes = req_args + [I32P, C.POINTER(TpResult)]
+    L.tp_global_optimum.argtypes = req_args + [I32P, C.POINTER(TpResult)]
     L.tp_allocate_batch.argtypes = [C.c_void_p, C.c_int32, C.POINTER(TpRequest), I32P, C.c_int32, I32P,
                                     C.POINTER(TpResult)]
     L.tp_search_shard.argtypes = req_args + [C.c_int32, C.c_int32, C.POINTER(TpKey), C.POINTER(TpResult)]
@@ -221,6 +222,18 @@ class BestEffortPolicy:
         if rc < 0:
             self._raise(rc)
         return _ids(out, rc)
+
+    def GlobalOptimum(self, available, required, size):
+        """tp_global_optimum: the best set over ALL subsets (advisory; not what the reference returns)."""
+        required = required or []
+        av, rq = self.indices(available), self.indices(required)
+        out = _i32([0] * max(size, 1))
+        res = TpResult()
+        rc = lib().tp_global_optimum(self.handle, _i32(av), len(av), _i32(rq), len(rq), size, out, C.byref(res))
+        self.last = res.dict()
+        if rc < 0:
+            raise AllocatorError(rc, strerror(rc))
+        return [self.devices[i].Id for i in out[:rc]]
 
     def SearchShard(self, available, required, size, shard_index, shard_count):
         """(key | None if short-circuited): this shard's packed winner."""

@@ -340,6 +340,30 @@ void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_
     if (!out.family_only && p->kernel != TP_KERNEL_LEX && build_plan(p, out)) out.kernel = TP_KERNEL_SPLIT;
 }
 
+// Advisory mode (tp_global_optimum): every free device becomes a group of its own, so Family holds
+// every subset and RefKey orders equal scores by canonical position; the canonical order itself
+// stays that of the real groups.  Re-decides the kernel for the new tables.
+int ungroup(const tp_policy *p, Prep &pr) {
+    TpReq &rq = pr.rq;
+    for (int i = 0; i < rq.n; i++) {
+        rq.group_of[i] = (uint8_t)i;
+        rq.gstart[i] = (uint8_t)i;
+        rq.gsize[i] = 1;
+    }
+    rq.n_groups = rq.n;
+    int dbits = 1;
+    while ((1 << dbits) < rq.n_groups) dbits++;
+    rq.dbits = dbits;
+    const u64 limit = p->exhaustive_limit ? p->exhaustive_limit : (1ull << 38);
+    if (rq.k > TP_MAX_K || rq.total > limit || rq.k * dbits > TP_SIGMA_BITS) return TP_ERR_TOO_LARGE;
+    pr.family_only = false;
+    pr.family_masks = 0;
+    pr.kernel = TP_KERNEL_LEX;
+    if (p->kernel == TP_KERNEL_AUTO && rq.total <= TP_FAST_MAX_SUBSETS) return 0;
+    if (p->kernel != TP_KERNEL_LEX && build_plan(p, pr)) pr.kernel = TP_KERNEL_SPLIT;
+    return 0;
+}
+
 // Winner key -> device indices in the reference's output order (besteffort_policy.go:141-148):
 // groups in sequence order, NodeId ascending inside a group, required last in request order.
 int decode(const Prep &pr, const TpKey &key, const int32_t *req, int32_t *out) {
@@ -639,6 +663,27 @@ int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32
     TpKey key;
     const bool fast = pr.kernel != TP_KERNEL_FAMILY && !pr.family_only && pr.rq.total <= TP_FAST_MAX_SUBSETS &&
                       p->kernel == TP_KERNEL_AUTO;
+    int rc = fast ? run_search_fast(p, lease.ctx(), pr, &key, info)
+                  : run_search(p, lease.ctx(), pr, 0, 1, 1, true, &key, info, nullptr);
+    if (rc) return rc;
+    return decode(pr, key, req, out);
+}
+
+int tp_global_optimum(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req,
+                      int32_t size, int32_t *out, tp_result *info) {
+    if (!p || !out) return TP_ERR_BAD_ARGUMENT;
+    if (info) memset(info, 0, sizeof *info);
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr);
+    if (pr.status) return pr.status;
+    if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; }
+    if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }
+    if (int rc = ungroup(p, pr)) return rc;
+    if (p->host_only) return TP_ERR_CUDA;
+    DeviceGuard guard(p->cuda_device);
+    CtxLease lease(p);
+    TpKey key;
+    const bool fast = pr.rq.total <= TP_FAST_MAX_SUBSETS && p->kernel == TP_KERNEL_AUTO;
     int rc = fast ? run_search_fast(p, lease.ctx(), pr, &key, info)
                   : run_search(p, lease.ctx(), pr, 0, 1, 1, true, &key, info, nullptr);
     if (rc) return rc;
