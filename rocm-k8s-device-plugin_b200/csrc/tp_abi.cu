@@ -59,7 +59,11 @@ struct Prep {
     bool family_only = false; // not enumerable and not within the FAMILY kernel's limits either
     u64 family_masks = 0;     // kernel FAMILY: 2^groups bitmasks to visit
     int shards = 1;           // how many shards the search will be split into (sizes the SPLIT items)
+    bool batch = false;       // prepared for tp_allocate_batch: a block, not the grid, takes each share
 };
+
+// tp_allocate_batch cuts a heavy SPLIT request into this many shares, each taken by one block.
+inline int batch_shares(u64 total) { return total <= (1ull << 24) ? 1 : (int)std::min<u64>(16, (total >> 24) + 1); }
 
 } // namespace
 
@@ -224,6 +228,10 @@ bool build_plan(const tp_policy *p, Prep &out) {
     // small (measured sweep on C4: 3.12 ms at 1K, 2.86 ms at 64K; at 8 shards 64K items leave a
     // 0.17 ms tail on a 0.37 ms shard).
     u64 cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (400000ull * (u64)std::max(out.shards, 1))), 65536);
+    // In a batch the eight warps of one block share a share: a handful of items per warp balances
+    // them, and larger items spend less on the per-item set-up (unrank, lane vectors).
+    if (out.batch)
+        cap0 = std::min<u64>(std::max<u64>(2048, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 6)), 65536);
     if (const char *env = getenv("TP_SPLIT_CAP")) cap0 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
     u64 items = 0;
     for (int e = 0; e < pl.n_entries; e++) {
@@ -246,8 +254,9 @@ bool build_plan(const tp_policy *p, Prep &out) {
 // The nine ordered checks and two short-circuits of Allocate (besteffort_policy.go:90-124),
 // then filterPartitions (device.go:310-351) as canonical order + group tables.
 void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
-             Prep &out, int shards = 1) {
+             Prep &out, int shards = 1, bool batch = false) {
     out.shards = shards;
+    out.batch = batch;
     out.status = 0;
     out.shortcut = 0;
     out.n_req = n_req;
@@ -769,7 +778,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         auto work = [&](int t) {
             for (int i = t; i < n_requests; i += nthreads)
                 prepare(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required, rqs[i].size,
-                        preps[i]);
+                        preps[i], 1, true);
         };
         std::vector<std::thread> pool;
         for (int t = 1; t < nthreads; t++) pool.emplace_back(work, t);
@@ -819,9 +828,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         // Heavy requests are cut into shares taken by different blocks (the same item striding as
         // multi-GPU shards), so that one big search does not become the tail of its group.
         auto shares_of = [&](int i) -> int {
-            if (preps[i].kernel != TP_KERNEL_SPLIT) return 1;
-            const u64 t = preps[i].rq.total;
-            return t <= (1ull << 24) ? 1 : (int)std::min<u64>(16, (t >> 24) + 1);
+            return preps[i].kernel == TP_KERNEL_SPLIT ? batch_shares(preps[i].rq.total) : 1;
         };
         size_t n_out = 0;
         std::vector<int> out_base(n_requests, -1);

@@ -42,6 +42,33 @@ static __device__ __noinline__ bool tp_family_key(u64 p0, u64 p1, int k, int sco
     return true;
 }
 
+// Can a subset still be a Family member when its `cnt` lowest canonical positions are the packed
+// ones and every remaining member lies at a canonical position >= first_future?  A hole below a
+// chosen member of a group can no longer be filled, and a group that ends before first_future
+// stays as it is: two such prefixes, or one non-prefix, rule the whole leaf out (necessary
+// condition only: tp_family_key decides).
+static __device__ __noinline__ bool tp_family_alive(u64 p0, u64 p1, int cnt, int first_future,
+                                                    const uint8_t *s_group, const uint8_t *s_gstart,
+                                                    const uint8_t *s_gsize) {
+    auto elem = [&](int i) { return (int)(((i < 8 ? p0 : p1) >> ((i & 7) * 8)) & 0xFF); };
+    int closed_partials = 0, i = 0;
+    while (i < cnt) {
+        const int e = elem(i);
+        const int g = s_group[e];
+        int j = i + 1;
+        while (j < cnt && s_group[elem(j)] == g) j++;
+        const int c = j - i, gs = s_gstart[g], gz = s_gsize[g];
+        if (c != gz) {
+            if (e != gs) return false;
+            for (int t = 1; t < c; t++)
+                if (elem(i + t) != e + t) return false;
+            if (gs + gz <= first_future && ++closed_partials > 1) return false;
+        }
+        i = j;
+    }
+    return true;
+}
+
 static __device__ __forceinline__ TpKey tp_warp_min_key(TpKey k) {
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) {

@@ -291,6 +291,25 @@ __device__ __forceinline__ int tp_split_va_get(const uint32_t *va, int lane, int
     return (j & 1) ? (int)(pk >> 16) : (int)(pk & 0xFFFF);
 }
 
+// The fixed part of a leaf (A, B'', leaf position; canonical ascending = positions descending)
+// against tp_family_alive: most leaves that merely tie with the bound die here, before any pair
+// of theirs is looked at.  The pairs come from positions < limit.
+static __device__ __noinline__ bool tp_split_leaf_alive(const TpSplitShared &sh, const TpSmem &s, const TpSplitWarp &w,
+                                                        int d_used, int b_leaf, int limit) {
+    u64 f0 = 0, f1 = 0;
+    int cnt = 0;
+    auto push = [&](int pos) {
+        const u64 c = (u64)(sh.n - 1 - pos);
+        if (cnt < 8) f0 |= c << (8 * cnt);
+        else f1 |= c << (8 * (cnt - 8));
+        cnt++;
+    };
+    for (int i = 0; i < sh.p; i++) push((int)(((i < 8 ? w.a0 : w.a1) >> (8 * (i & 7))) & 0xFF));
+    for (int i = 0; i + 1 < d_used; i++) push(w.bstack[i]);
+    if (d_used > 0) push(b_leaf);
+    return tp_family_alive(f0, f1, cnt, sh.n - limit, s.group, s.gstart, s.gsize);
+}
+
 // Re-walk one leaf for one lane with scalar arithmetic and apply Family/RefKey to every pair
 // that scores no worse than the bound.  base = c_req + sA + cross(A,B'') + score inside B''.
 template <int M>
@@ -304,6 +323,7 @@ __device__ __noinline__ void tp_split_slow(const TpSplitShared &sh, const TpSmem
         if (d_used > 0) v += sh.wp[b_leaf * sh.rsp + j];
         return v;
     };
+    if (!tp_split_leaf_alive(sh, s, w, d_used, b_leaf, limit)) return;
     // Stage the lane's P values once, then visit only rows that can still reach the bound:
     // row jx needs P[jx] + min_{jy<jx} P[jy] + (smallest pair weight) <= bound - base.
     int pv[TP_MAX_N];
@@ -403,6 +423,56 @@ struct TpSplitWalk {
     }
 };
 
+// Exact seed for requests with few groups: the block scores every Family member (whole groups by
+// bitmask, plus at most one lowest-NodeId prefix of another group), so the scan starts from the
+// optimal Family score and only ties -- and non-members below it -- ever reach the slow path.
+// Without it a search that is all "first leaves" (thousands of warps starting at once from the
+// two cheap seeds) spends most of its time re-walking leaves that a better bound would skip.
+#define TP_SEED_MAX_GROUPS 14
+static __device__ __noinline__ void tp_split_family_seed(const TpSmem &s, int n_groups, int k, int c_req, int *s_bound) {
+    if (n_groups > TP_SEED_MAX_GROUPS) return;
+    const unsigned n_masks = 1u << n_groups;
+    int best = 0x7FFFFFFF;
+    for (unsigned mask = threadIdx.x; mask < n_masks; mask += blockDim.x) {
+        int pos[TP_MAX_K];
+        int cnt = 0;
+        bool over = false;
+        for (unsigned m = mask; m; m &= m - 1) {
+            const int g = __ffs(m) - 1;
+            const int gz = s.gsize[g], gs = s.gstart[g];
+            if (cnt + gz > k) {
+                over = true;
+                break;
+            }
+            for (int t = 0; t < gz; t++) pos[cnt++] = gs + t;
+        }
+        if (over) continue;
+        int base = c_req;
+        for (int i = 0; i < cnt; i++) {
+            base += s.u[pos[i]];
+            for (int j = 0; j < i; j++) base += s.w[pos[j] * s.stride + pos[i]];
+        }
+        if (cnt == k) {
+            best = min(best, base);
+            continue;
+        }
+        const int r = k - cnt; // devices still to take: a proper prefix of one more group
+        for (int h = 0; h < n_groups; h++) {
+            if (((mask >> h) & 1u) || s.gsize[h] <= r) continue;
+            const int hs = s.gstart[h];
+            int sco = base;
+            for (int t = 0; t < r; t++) {
+                const int x = hs + t;
+                sco += s.u[x];
+                for (int i = 0; i < cnt; i++) sco += s.w[pos[i] * s.stride + x];
+                for (int t2 = 0; t2 < t; t2++) sco += s.w[(hs + t2) * s.stride + x];
+            }
+            best = min(best, sco);
+        }
+    }
+    if (best != 0x7FFFFFFF) atomicMin(s_bound, best);
+}
+
 // The search of one request by the calling block: items are handed out through *work_counter
 // (a global word shared by the grid, or a shared-memory word when the block owns the request).
 // Not inlined on purpose: the kernel's request loop must not compete with it for registers.
@@ -456,8 +526,9 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
             sco += s.u[pos[i]];
             for (int j = 0; j < i; j++) sco += s.w[pos[j] * s.stride + pos[i]];
         }
-        if (left == 0 && sco < s_bound) s_bound = sco;
+        if (left == 0 && sco < s_bound) atomicMin(&s_bound, sco);
     }
+    tp_split_family_seed(s, rq->n_groups, k, rq->c_req, &s_bound);
     __syncthreads();
     for (int i = lane; i < M; i += 32) tstack[i] = t0[i];
     __syncwarp();
