@@ -388,25 +388,33 @@ struct TpSplitWalk {
             const uint4 *wm4 = (const uint4 *)tp_split_smem;
             const uint4 *v4 = (const uint4 *)w.va + w.lane;
             const int room = *(volatile int *)s_bound - lb - sb + 1; // > score of (b, pair) <=> no candidate
-            unsigned Pa[TP_SPLIT_PB + TP_SPLIT_DUAL_M / 2];
+            // (a lane without a real A never reports: its threshold is 0)
+            const unsigned room2 = w.active ? (unsigned)min(max(room, 0), 0xFFFF) * 0x10001u : 0u;
             int b = hi - 1;
             while (b >= lo) {
-                if (b <= TP_SPLIT_DUAL_M) { // (a leftover single leaf drags a dummy partner b-1 >= 1 along)
-                    // leaves b and b-1 together (P doubles as the first leaf's vector)
-                    tp_split_make_p2<M>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS),
-                                        (const uint4 *)(sh.wm + (b - 1) * Cfg::RS), b);
-                    unsigned runa, runb;
-                    tp_split_pairs2<M>(P, wm4, b - 1, runa, runb);
-                    const int va_a = tp_split_va_get(w.va, w.lane, b), va_b = tp_split_va_get(w.va, w.lane, b - 1);
-                    const int ta = tl[b], tb = tl[b - 1];
-                    const unsigned thra = (unsigned)min(max(room - va_a - ta, 0), 0xFFFF) * 0x10001u;
-                    const unsigned thrb = (unsigned)min(max(room - va_b - tb, 0), 0xFFFF) * 0x10001u;
-                    if (__vminu2(runa, thra) != thra && w.active)
-                        tp_split_slow<M>(sh, s, w, D, b, b, lb + va_a + sb + ta, s_bound, best);
-                    if (__vminu2(runb, thrb) != thrb && w.active && b - 1 >= lo)
-                        tp_split_slow<M>(sh, s, w, D, b - 1, b - 1, lb + va_b + sb + tb, s_bound, best);
-                    b -= 2;
-                    continue;
+                if ((b | 1) <= TP_SPLIT_DUAL_M) {
+                    // Leaves top and top-1 together, top odd: the two positions then share one packed
+                    // word of V and of T, so one add yields both leaves' own terms and one packed
+                    // compare decides for both.  An even first leaf drags the dummy top = hi along
+                    // and a last one the dummy top-1 < lo; both are turned away on the rare path.
+                    for (int top = b | 1; top >= lo; top -= 2) {
+                        tp_split_make_p2<M>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + top * Cfg::RS),
+                                            (const uint4 *)(sh.wm + (top - 1) * Cfg::RS), top);
+                        unsigned runa, runb;
+                        tp_split_pairs2<M>(P, wm4, top - 1, runa, runb);
+                        const int h = top >> 1;
+                        const unsigned vt = ((const uint32_t *)v4)[(h >> 2) * 128 + (h & 3)] + ((const uint32_t *)tl)[h];
+                        const unsigned ta = runa + __byte_perm(vt, 0, 0x3232); // + (V+T)[top] in both halves
+                        const unsigned tb = runb + __byte_perm(vt, 0, 0x1010); // + (V+T)[top-1]
+                        if (__vminu2(__vminu2(ta, tb), room2) != room2) {
+                            if (__vminu2(ta, room2) != room2 && top < hi)
+                                tp_split_slow<M>(sh, s, w, D, top, top, lb + sb + (int)(vt >> 16), s_bound, best);
+                            if (__vminu2(tb, room2) != room2 && top - 1 >= lo)
+                                tp_split_slow<M>(sh, s, w, D, top - 1, top - 1, lb + sb + (int)(vt & 0xFFFF), s_bound,
+                                                 best);
+                        }
+                    }
+                    break;
                 }
                 if constexpr (M > TP_SPLIT_DUAL_M) { // positions above 64: one leaf at a time
                     tp_split_make_p<M, true>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + b * Cfg::RS), b);
