@@ -277,6 +277,51 @@ __device__ __forceinline__ void tp_split_make_p2(unsigned (&Pa)[TP_SPLIT_PREGS],
     }
 }
 
+// ---- the six smallest leaves at once ----------------------------------------------------------
+// A leaf at position b holds only C(b,2) pairs, and most leaves are small (the average leaf
+// position is about n / (k'-1)), so for them the per-leaf work around the rows (dispatch, lane
+// vector loads, threshold) outweighs the rows.  Leaves 2..7 live entirely in the first 16-byte
+// chunk of every vector: this block scores all six with compile-time positions -- V+T loaded once,
+// seven row chunks loaded once, no dispatch -- and returns the packed minimum of
+// res[b] = (min over the leaf's pairs) + (V+T)[b].
+template <int M>
+__device__ __forceinline__ unsigned tp_split_tail(const uint4 *__restrict__ v4, const uint4 *__restrict__ t4,
+                                                  const uint4 *__restrict__ wm4, unsigned (&res)[8],
+                                                  unsigned (&vt)[4]) {
+    const uint4 v = v4[0], t = t4[0];
+    vt[0] = v.x + t.x;
+    vt[1] = v.y + t.y;
+    vt[2] = v.z + t.z;
+    vt[3] = v.w + t.w;
+    unsigned row[8][4];
+#pragma unroll
+    for (int j = 1; j < 8; j++) {
+        const uint4 r = wm4[j * TpSplitCfg<M>::RS4]; // positions 0..7 of row j, TP_BIG at jy >= j
+        row[j][0] = r.x;
+        row[j][1] = r.y;
+        row[j][2] = r.z;
+        row[j][3] = r.w;
+    }
+    unsigned m = 0xFFFFFFFFu;
+#pragma unroll
+    for (int b = 2; b < 8; b++) {
+        unsigned Pb[4];
+#pragma unroll
+        for (int r = 0; r < (b + 1) / 2; r++) Pb[r] = vt[r] + row[b][r];
+        unsigned run = TP_BIG2 + TP_BIG2;
+#pragma unroll
+        for (int jx = 1; jx < b; jx++) {
+            unsigned acc = TP_BIG2 + TP_BIG2;
+#pragma unroll
+            for (int r = 0; r < (jx + 1) / 2; r++) acc = __viaddmin_u16x2(Pb[r], row[jx][r], acc);
+            run = __viaddmin_u16x2(acc, __byte_perm(Pb[jx / 2], 0, (jx & 1) ? 0x3232 : 0x1010), run);
+        }
+        res[b] = run + __byte_perm(vt[b / 2], 0, (b & 1) ? 0x3232 : 0x1010);
+        m = __vminu2(m, res[b]);
+    }
+    return m;
+}
+
 struct TpSplitWarp { // per-warp state (uniform unless noted)
     uint16_t *tstack;   // [D+1][M] level vectors
     uint32_t *va;       // [M/8][32][4] lane-private V, packed pairs, 16 bytes per lane per chunk
@@ -397,7 +442,9 @@ struct TpSplitWalk {
                     // word of V and of T, so one add yields both leaves' own terms and one packed
                     // compare decides for both.  An even first leaf drags the dummy top = hi along
                     // and a last one the dummy top-1 < lo; both are turned away on the rare path.
-                    for (int top = b | 1; top >= lo; top -= 2) {
+                    const bool tail = lo == 2 && hi > 7; // leaves 2..7 are all there: scored in one block below
+                    const int stop = tail ? 9 : lo;
+                    for (int top = b | 1; top >= stop; top -= 2) {
                         tp_split_make_p2<M>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + top * Cfg::RS),
                                             (const uint4 *)(sh.wm + (top - 1) * Cfg::RS), top);
                         unsigned runa, runb;
@@ -412,6 +459,18 @@ struct TpSplitWalk {
                             if (__vminu2(tb, room2) != room2 && top - 1 >= lo)
                                 tp_split_slow<M>(sh, s, w, D, top - 1, top - 1, lb + sb + (int)(vt & 0xFFFF), s_bound,
                                                  best);
+                        }
+                    }
+                    if (tail) {
+                        unsigned res[8], vt[4];
+                        const unsigned m = tp_split_tail<M>(v4, (const uint4 *)tl, wm4, res, vt);
+                        if (__vminu2(m, room2) != room2) {
+#pragma unroll
+                            for (int lb7 = 7; lb7 >= 2; lb7--)
+                                if (__vminu2(res[lb7], room2) != room2)
+                                    tp_split_slow<M>(sh, s, w, D, lb7, lb7,
+                                                     lb + sb + (int)((vt[lb7 / 2] >> (16 * (lb7 & 1))) & 0xFFFF), s_bound,
+                                                     best);
                         }
                     }
                     break;
