@@ -322,6 +322,67 @@ __device__ __forceinline__ unsigned tp_split_tail(const uint4 *__restrict__ v4, 
     return m;
 }
 
+// Leaves 8..11 the same way (two chunks per vector): rows are loaded once for the four leaves.
+template <int M>
+__device__ __forceinline__ unsigned tp_split_mid(const uint4 *__restrict__ v4, const uint4 *__restrict__ t4,
+                                                 const uint4 *__restrict__ wm4, const unsigned (&vt0)[4],
+                                                 unsigned (&res)[4], unsigned (&vt1)[4]) {
+    constexpr int RS4 = TpSplitCfg<M>::RS4;
+    const uint4 v = v4[32], t = t4[1];
+    vt1[0] = v.x + t.x;
+    vt1[1] = v.y + t.y;
+    vt1[2] = v.z + t.z;
+    vt1[3] = v.w + t.w;
+    unsigned Pb[4][6], run[4];
+#pragma unroll
+    for (int i = 0; i < 4; i++) { // leaf b = 8 + i: positions 0..7, and 8..b-1 from the second chunk
+        const int b = 8 + i;
+        const uint4 r0 = wm4[b * RS4];
+        Pb[i][0] = vt0[0] + r0.x;
+        Pb[i][1] = vt0[1] + r0.y;
+        Pb[i][2] = vt0[2] + r0.z;
+        Pb[i][3] = vt0[3] + r0.w;
+        if (i > 0) {
+            const uint2 r1 = ((const uint2 *)(wm4 + b * RS4 + 1))[0];
+            Pb[i][4] = vt1[0] + r1.x;
+            if (i > 2) Pb[i][5] = vt1[1] + r1.y;
+        }
+        run[i] = TP_BIG2 + TP_BIG2;
+    }
+#pragma unroll
+    for (int jx = 10; jx >= 1; jx--) {
+        unsigned row[6];
+        {
+            const uint4 r = wm4[jx * RS4];
+            row[0] = r.x;
+            row[1] = r.y;
+            row[2] = r.z;
+            row[3] = r.w;
+            if (jx > 8) {
+                const uint2 r1 = ((const uint2 *)(wm4 + jx * RS4 + 1))[0];
+                row[4] = r1.x;
+                row[5] = r1.y;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (8 + i > jx) {
+                unsigned acc = TP_BIG2 + TP_BIG2;
+#pragma unroll
+                for (int r = 0; r < (jx + 1) / 2; r++) acc = __viaddmin_u16x2(Pb[i][r], row[r], acc);
+                run[i] = __viaddmin_u16x2(acc, __byte_perm(Pb[i][jx / 2], 0, (jx & 1) ? 0x3232 : 0x1010), run[i]);
+            }
+        }
+    }
+    unsigned m = 0xFFFFFFFFu;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        res[i] = run[i] + __byte_perm(vt1[i / 2], 0, (i & 1) ? 0x3232 : 0x1010);
+        m = __vminu2(m, res[i]);
+    }
+    return m;
+}
+
 struct TpSplitWarp { // per-warp state (uniform unless noted)
     uint16_t *tstack;   // [D+1][M] level vectors
     uint32_t *va;       // [M/8][32][4] lane-private V, packed pairs, 16 bytes per lane per chunk
@@ -443,7 +504,8 @@ struct TpSplitWalk {
                     // compare decides for both.  An even first leaf drags the dummy top = hi along
                     // and a last one the dummy top-1 < lo; both are turned away on the rare path.
                     const bool tail = lo == 2 && hi > 7; // leaves 2..7 are all there: scored in one block below
-                    const int stop = tail ? 9 : lo;
+                    const bool mid = tail && hi > 11;    // ... and so are leaves 8..11
+                    const int stop = mid ? 13 : tail ? 9 : lo;
                     for (int top = b | 1; top >= stop; top -= 2) {
                         tp_split_make_p2<M>(P, v4, (const uint4 *)tl, (const uint4 *)(sh.wm + top * Cfg::RS),
                                             (const uint4 *)(sh.wm + (top - 1) * Cfg::RS), top);
@@ -464,6 +526,18 @@ struct TpSplitWalk {
                     if (tail) {
                         unsigned res[8], vt[4];
                         const unsigned m = tp_split_tail<M>(v4, (const uint4 *)tl, wm4, res, vt);
+                        if (mid) {
+                            unsigned res1[4], vt1[4];
+                            const unsigned m1 = tp_split_mid<M>(v4, (const uint4 *)tl, wm4, vt, res1, vt1);
+                            if (__vminu2(m1, room2) != room2) {
+#pragma unroll
+                                for (int i = 3; i >= 0; i--)
+                                    if (__vminu2(res1[i], room2) != room2)
+                                        tp_split_slow<M>(sh, s, w, D, 8 + i, 8 + i,
+                                                         lb + sb + (int)((vt1[i / 2] >> (16 * (i & 1))) & 0xFFFF), s_bound,
+                                                         best);
+                            }
+                        }
                         if (__vminu2(m, room2) != room2) {
 #pragma unroll
                             for (int lb7 = 7; lb7 >= 2; lb7--)
