@@ -199,7 +199,8 @@ bool build_plan(const tp_policy *p, Prep &out) {
     const TpReq &rq = out.rq;
     const int n = rq.n, k = rq.k;
     if (k < 4 || k > TP_MAX_K) return false;
-    const int q = k >= 6 ? std::min(k - 4, TP_SPLIT_MAX_D + 2) : 2;
+    int q = k >= 6 ? std::min(k - 4, TP_SPLIT_MAX_D + 2) : 2;
+    if (const char *env = getenv("TP_SPLIT_Q")) q = std::max(2, std::min({atoi(env), k - 1, TP_SPLIT_MAX_D + 2})); // tuning aid
     const int pp = k - q;
     if (pp > TP_SPLIT_MAX_P || n - pp > TP_SPLIT_MAX_M || n - pp < q) return false;
     int max_w = 0, max_u = 0, min_w = 255;

@@ -491,7 +491,9 @@ struct TpSplitWalk {
             }
         } else {
             // leaf level: b is the last walked position, the pairs live below it
-            const uint4 *wm4 = (const uint4 *)tp_split_smem;
+            // (sh.wm is the start of shared memory; going through the field rather than the symbol keeps
+            // the table base in a register instead of re-deriving the shared window address per load)
+            const uint4 *wm4 = (const uint4 *)sh.wm;
             const uint4 *v4 = (const uint4 *)w.va + w.lane;
             const int room = *(volatile int *)s_bound - lb - sb + 1; // > score of (b, pair) <=> no candidate
             // (a lane without a real A never reports: its threshold is 0)
@@ -631,7 +633,9 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // layout: masked table first (its row chunks are then compile-time offsets from the start of
     // shared memory), then the staged request, the plain table, u, and the per-warp areas
-    uint16_t *wm = (uint16_t *)smem;
+    // (+ a zero the compiler cannot see: the base then lives in a register and rows are addressed
+    // [base + constant]; from the bare symbol every load re-derives the shared window address)
+    uint16_t *wm = (uint16_t *)smem + (plan->p >> 24);
     size_t off = (size_t)n * Cfg::RS * 2;
     const TpSmem s = tp_smem_carve(smem + off, n, k);
     tp_stage_request(s, W, nd, binom_g, rq, k, &s_bound);
