@@ -419,7 +419,9 @@ static __device__ __noinline__ bool tp_split_leaf_alive(const TpSplitShared &sh,
 // Re-walk one leaf for one lane with scalar arithmetic and apply Family/RefKey to every pair
 // that scores no worse than the bound.  base = c_req + sA + cross(A,B'') + score inside B''.
 template <int M>
-__device__ __noinline__ void tp_split_slow(const TpSplitShared &sh, const TpSmem &s, const TpSplitWarp &w,
+// (The three descriptors come by value: handing out their addresses would pin the caller's copies
+// to local memory and make the hot loop reload them after every possible call.)
+__device__ __noinline__ void tp_split_slow(const TpSplitShared sh, const TpSmem s, const TpSplitWarp w,
                                            int d_used, int b_leaf, int limit, int base, int *s_bound,
                                            TpKey &best) {
     const int n = sh.n;
@@ -572,7 +574,7 @@ struct TpSplitWalk {
 // Without it a search that is all "first leaves" (thousands of warps starting at once from the
 // two cheap seeds) spends most of its time re-walking leaves that a better bound would skip.
 #define TP_SEED_MAX_GROUPS 14
-static __device__ __noinline__ void tp_split_family_seed(const TpSmem &s, int n_groups, int k, int c_req, int *s_bound) {
+static __device__ __noinline__ void tp_split_family_seed(const TpSmem s, int n_groups, int k, int c_req, int *s_bound) {
     if (n_groups > TP_SEED_MAX_GROUPS) return;
     const unsigned n_masks = 1u << n_groups;
     int best = 0x7FFFFFFF;
