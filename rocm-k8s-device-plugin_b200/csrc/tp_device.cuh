@@ -197,18 +197,23 @@ static __host__ __device__ size_t tp_smem_bytes(int n, int K) {
 static __device__ void tp_stage_request(const TpSmem &s, const uint8_t *__restrict__ W, int nd,
                                  const u64 *__restrict__ binom_g, const TpReq *__restrict__ rq, int K,
                                  int *s_bound) {
+    // Rows by warp, columns by lane: no integer division, and the canonical order is read from
+    // shared memory instead of twice per element from the descriptor.
+    __shared__ uint8_t s_canon[TP_MAX_N];
     const int n = rq->n, tid = threadIdx.x, nt = blockDim.x;
-    for (int i = tid; i < (n + 1) * (K + 1); i += nt) {
-        const int a = i / (K + 1), j = i - a * (K + 1);
-        s.binom[i] = binom_g[a * TP_BINOM_COLS + j];
-    }
-    for (int i = tid; i < n * n; i += nt) {
-        const int r = i / n, c = i - r * n;
-        s.w[r * s.stride + c] = (r == c) ? 0 : W[(int)rq->canon[r] * nd + rq->canon[c]];
+    const int warp = tid >> 5, lane = tid & 31, nw = nt >> 5;
+    for (int i = tid; i < n; i += nt) s_canon[i] = rq->canon[i];
+    for (int a = warp; a <= n; a += nw)
+        for (int j = lane; j <= K; j += 32) s.binom[a * (K + 1) + j] = binom_g[a * TP_BINOM_COLS + j];
+    __syncthreads();
+    for (int r = warp; r < n; r += nw) {
+        const uint8_t *wrow = W + (int)s_canon[r] * nd;
+        for (int c = lane; c < n; c += 32) s.w[r * s.stride + c] = (r == c) ? 0 : wrow[s_canon[c]];
     }
     for (int i = tid; i < n; i += nt) {
+        const uint8_t *wrow = W + (int)s_canon[i] * nd;
         int u = 0;
-        for (int r = 0; r < rq->n_req; r++) u += W[(int)rq->canon[i] * nd + rq->req[r]];
+        for (int r = 0; r < rq->n_req; r++) u += wrow[rq->req[r]];
         s.u[i] = (uint16_t)u;
         s.group[i] = rq->group_of[i];
         s.gstart[i] = rq->gstart[i];
@@ -225,4 +230,3 @@ static __device__ void tp_stage_request(const TpSmem &s, const uint8_t *__restri
     }
     __syncthreads();
 }
-

@@ -652,13 +652,12 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
     uint16_t *tstack = (uint16_t *)warp_base;                             // [D+1][M]
     uint32_t *va = (uint32_t *)(warp_base + (size_t)(D + 1) * M * 2);     // [M/8][32][4]
     uint8_t *bstack = (uint8_t *)(va + Cfg::NCHUNK * 32 * 4);             // [<=16]
-    for (int i = threadIdx.x; i < n * rsp; i += blockDim.x) { // plain table, padding 0 (it is summed)
-        const int j = i / rsp, jj = i - j * rsp;
-        wp[i] = (jj < n && jj != j) ? (uint16_t)s.w[(n - 1 - j) * s.stride + (n - 1 - jj)] : (uint16_t)0;
-    }
-    for (int i = threadIdx.x; i < n * Cfg::RS; i += blockDim.x) { // masked table, padding BIG
-        const int j = i / Cfg::RS, jj = i - j * Cfg::RS;
-        wm[i] = (jj < j && jj < n) ? (uint16_t)s.w[(n - 1 - j) * s.stride + (n - 1 - jj)] : (uint16_t)TP_BIG;
+    for (int j = warp; j < n; j += TP_SPLIT_WARPS) { // one table row per warp pass: no divisions
+        const uint8_t *src = s.w + (n - 1 - j) * s.stride + (n - 1);
+        for (int jj = lane; jj < rsp; jj += 32) // plain table, padding 0 (it is summed)
+            wp[j * rsp + jj] = (jj < n && jj != j) ? (uint16_t)src[-jj] : (uint16_t)0;
+        for (int jj = lane; jj < Cfg::RS; jj += 32) // masked table, padding BIG
+            wm[j * Cfg::RS + jj] = (jj < j && jj < n) ? (uint16_t)src[-jj] : (uint16_t)TP_BIG;
     }
     for (int i = threadIdx.x; i < TP_MAX_N; i += blockDim.x) t0[i] = i < n ? s.u[n - 1 - i] : (uint16_t)0;
     if (threadIdx.x == 0) { // second seed: whole groups from the largest down (also a Family member)
