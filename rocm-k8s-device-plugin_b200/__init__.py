@@ -18,7 +18,7 @@ import os
 from dataclasses import dataclass
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libtpalloc.so")
+LIB_PATH = os.environ.get("TP_ALLOC_LIB") or os.path.join(_HERE, "libtpalloc.so")  # (override: A/B runs of two builds)
 ID_LEN = 64
 
 TP_MAX_DEVICES = 128

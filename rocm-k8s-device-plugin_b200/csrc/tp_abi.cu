@@ -234,6 +234,24 @@ bool build_plan(const tp_policy *p, Prep &out) {
     if (out.batch)
         cap0 = std::min<u64>(std::max<u64>(2048, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 6)), 65536);
     if (const char *env = getenv("TP_SPLIT_CAP")) cap0 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
+    // Single values of b0 become items of their own, cut by b1 (D >= 2 only) -- only where it matters:
+    // when one value alone is more than a quarter of what a lane has to do in this search (shard);
+    // restricted b1 ranges lose the compile-time leaf blocks and add per-item set-up.
+    pl.b_star = TP_MAX_N + 1;
+    if (q > 3) {
+        const u64 lanes = (u64)p->sm_count * 2 * TP_SPLIT_THREADS;
+        u64 cap1 = std::max<u64>(cap0, rq.total / (lanes * (u64)std::max(out.shards, 1) * 4));
+        if (out.batch) cap1 = std::max<u64>(cap0, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 4));
+        if (const char *env = getenv("TP_SPLIT_CAP1")) cap1 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
+        int bs = q - 1;
+        while (bs < n && p->binom[bs][q - 1] <= cap1) bs++;
+        pl.b_star = bs;
+        pl.cum[bs] = 0;
+        for (int b = bs; b <= n && b <= TP_MAX_N; b++) {
+            const u64 nsub = std::min<u64>(std::max<u64>((p->binom[b][q - 1] + cap1 - 1) / cap1, 1), TP_SPLIT_MAX_SUB);
+            pl.cum[b + 1] = (uint16_t)(pl.cum[b] + nsub);
+        }
+    }
     u64 items = 0;
     for (int e = 0; e < pl.n_entries; e++) {
         const int jt = pl.jt_hi - e;
@@ -241,11 +259,13 @@ bool build_plan(const tp_policy *p, Prep &out) {
         const u64 chunks = (na + 31) / 32;
         if (chunks == 0 || chunks > 0xFFFFFFFFull) return false;
         int np = 1; // slices of the first walked position, each about `cap0` subsets per lane
-        if (q > 2) np = (int)std::min<u64>(std::max<u64>((p->binom[jt][q] + cap0 - 1) / cap0, 1), TP_SPLIT_MAX_PIECES);
+        const int jlow = std::min(jt, (int)pl.b_star);
+        if (q > 2) np = (int)std::min<u64>(std::max<u64>((p->binom[jlow][q] + cap0 - 1) / cap0, 1), TP_SPLIT_MAX_PIECES);
+        const u64 top = jt > pl.b_star ? pl.cum[jt] : 0; // sub-slices of the single values b_star .. jt-1
         pl.item_base[e] = (uint32_t)items;
         pl.n_chunks[e] = (uint32_t)chunks;
         pl.n_pieces[e] = (uint8_t)np;
-        items += chunks * (u64)np;
+        items += chunks * ((u64)np + top);
         if (items > 0xFFFFFFF0ull) return false;
     }
     pl.total_items = (uint32_t)items;
@@ -409,7 +429,7 @@ cudaError_t upload_request(Ctx &c, const Prep &pr) {
     return cudaMemcpyAsync(c.d_req, c.h_req, bytes, cudaMemcpyHostToDevice, c.stream);
 }
 
-// Does shard (idx of cnt) hold any work?  LEX shards by rank range, SPLIT by item stride.
+// Does shard (idx of cnt) hold any work?  LEX shards by rank range, SPLIT by rotating item stride.
 bool shard_nonempty(const Prep &pr, int idx, int cnt) {
     if (pr.kernel == TP_KERNEL_SPLIT) return (u64)idx < pr.plan.total_items;
     u64 lo, hi;
@@ -432,15 +452,21 @@ u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
     for (int e = 0; e < pl.n_entries; e++) {
         const int jt = pl.jt_hi - e;
         const u64 na = p->binom[n - 1 - jt][pl.p - 1];
-        for (int piece = 0; piece < pl.n_pieces[e]; piece++) {
-            auto Cb = [&](int a, int b) -> u64 { return p->binom[a][b]; };
-            const int np = pl.n_pieces[e];
-            const u64 per_lane = pl.q == 2 ? p->binom[jt][2]
-                                           : p->binom[tp_split_cut(Cb, jt, pl.q, np, piece + 1)][pl.q] -
-                                                 p->binom[tp_split_cut(Cb, jt, pl.q, np, piece)][pl.q];
+        auto Cb = [&](int a, int b) -> u64 { return p->binom[a][b]; };
+        auto cum = [&](int b) -> int { return pl.cum[b]; };
+        const int np = pl.n_pieces[e];
+        const int n_slices = np + (jt > pl.b_star ? pl.cum[jt] : 0);
+        for (int slice = 0; slice < n_slices; slice++) {
+            TpSlice sl;
+            u64 per_lane = p->binom[jt][2]; // q == 2: every pair below the pivot
+            if (pl.q > 2) {
+                if (!tp_split_slice(Cb, cum, jt, pl.q, np, pl.b_star, slice, sl)) continue;
+                per_lane = sl.cut_again ? p->binom[sl.b1_hi][pl.q - 1] - p->binom[sl.b1_lo][pl.q - 1]
+                                        : p->binom[sl.b0_hi][pl.q] - p->binom[sl.b0_lo][pl.q];
+            }
             for (u64 ac = 0; ac < pl.n_chunks[e]; ac++) {
-                const u64 item = pl.item_base[e] + (u64)piece * pl.n_chunks[e] + ac;
-                if (item % (unsigned)cnt != (unsigned)idx) continue;
+                const u64 item = pl.item_base[e] + (u64)slice * pl.n_chunks[e] + ac;
+                if ((item + item / (unsigned)cnt) % (unsigned)cnt != (unsigned)idx) continue; // as tp_split_search
                 sum += per_lane * std::min<u64>(32, na - ac * 32);
             }
         }

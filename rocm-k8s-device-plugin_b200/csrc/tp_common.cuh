@@ -128,7 +128,13 @@ struct TpBatch { // count == 0: single-request mode (all blocks share request 0,
 #define TP_SPLIT_MAX_D 4
 #define TP_SPLIT_SCORE_LIMIT 12000 /* every partial sum must stay below TP_BIG */
 
-// Work plan: items = (pivot, chunk of 32 lane sets, slice of the first walked position).
+// Work plan: items = (pivot, chunk of 32 lane sets, slice).  Item index inside pivot entry e:
+// slice * n_chunks[e] + chunk.  The slices of a pivot jt are
+//   * n_pieces[e] equal-work slices of the first walked position b0 over [q-1, min(jt, b_star)), then
+//   * every single value b0 in [b_star, jt), cut into cum[b0+1] - cum[b0] equal-work parts of the
+//     second walked position b1: one b0 is the finest grain of the first kind, and at the top
+//     pivots one b0 still holds tens of thousands of subsets per lane (one warp, serial), which
+//     becomes the tail of a shard or of a mid-size search.
 struct TpPlan {
     int32_t p, q;         // |A|, |B''| + 2
     int32_t jt_hi;        // pivots run from jt_hi = n - p down to q
@@ -137,7 +143,16 @@ struct TpPlan {
     int32_t min_w;        // smallest weight between two free devices
     uint32_t item_base[TP_MAX_N]; // entry e <-> pivot jt_hi - e
     uint32_t n_chunks[TP_MAX_N];  // chunks of 32 A's
-    uint8_t n_pieces[TP_MAX_N];   // slices of the first walked position, see tp_split_cut
+    uint8_t n_pieces[TP_MAX_N];   // slices of the first walked position below b_star, see tp_split_cut
+    int32_t b_star;               // values b0 >= b_star are items of their own, cut again (see cum)
+    uint16_t cum[TP_MAX_N + 2];   // cum[b] = sub-slices of the single values b_star .. b-1
+};
+#define TP_SPLIT_MAX_SUB 16
+
+struct TpSlice {
+    int b0_lo, b0_hi; // first walked position in [b0_lo, b0_hi)
+    int b1_lo, b1_hi; // second walked position, further restricted when cut_again
+    bool cut_again;
 };
 
 // Slice i of np of the first walked position b0 in [q-1, jt): boundaries put about the same number
@@ -157,4 +172,35 @@ __host__ __device__ inline int tp_split_cut(BinomFn C, int jt, int q, int np, in
     return lo;
 }
 
-
+// Slice number -> ranges of the first two walked positions; false when the slice is empty.
+// Shared by the kernel (item -> work) and the host (counting what a shard scores).
+template <class BinomFn, class CumFn>
+__host__ __device__ inline bool tp_split_slice(BinomFn C, CumFn cum, int jt, int q, int np, int b_star, int slice,
+                                               TpSlice &o) {
+    o.b1_lo = 0;
+    o.b1_hi = TP_MAX_N;
+    o.cut_again = false;
+    if (slice < np) {
+        const int jlow = jt < b_star ? jt : b_star;
+        o.b0_lo = tp_split_cut(C, jlow, q, np, slice);
+        o.b0_hi = tp_split_cut(C, jlow, q, np, slice + 1);
+        return o.b0_lo < o.b0_hi;
+    }
+    const int t = slice - np;
+    int lo = b_star, hi = jt; // largest b in [b_star, jt) with cum(b) <= t
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((int)cum(mid) <= t) lo = mid;
+        else hi = mid;
+    }
+    const int nsub = (int)cum(lo + 1) - (int)cum(lo), sub = t - (int)cum(lo);
+    o.b0_lo = lo;
+    o.b0_hi = lo + 1;
+    if (nsub > 1) {
+        o.b1_lo = tp_split_cut(C, lo, q - 1, nsub, sub);
+        o.b1_hi = tp_split_cut(C, lo, q - 1, nsub, sub + 1);
+        o.cut_again = true;
+        return o.b1_lo < o.b1_hi;
+    }
+    return true;
+}

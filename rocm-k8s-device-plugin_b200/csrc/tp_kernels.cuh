@@ -15,7 +15,7 @@ struct TpLaunchInfo {
     int threads;
 };
 
-// Kernel SPLIT: shard s of P scores the plan's items s, s+P, ...; d_counter is a zeroable word
+// Kernel SPLIT: shard s of P scores the plan's items i with (i + i/P) mod P == s; d_counter is a zeroable word
 // of scratch used to hand out items.  Needs n - plan.p <= TP_SPLIT_MAX_M.
 #define TP_SPLIT_MAX_M 128
 cudaError_t tp_launch_exhaustive_split(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,

@@ -22,7 +22,7 @@
 //     LEX kernel does (tp_family_key).
 //
 // Work = items (pivot jt, chunk of 32 A's, slice of the first B'' position), heaviest first,
-// handed out by an atomic counter; shard s of P takes items s, s+P, ...
+// handed out by an atomic counter; shard s of P takes the items i with (i + i/P) mod P == s.
 #pragma once
 #include "tp_device.cuh"
 
@@ -386,7 +386,7 @@ __device__ __forceinline__ unsigned tp_split_mid(const uint4 *__restrict__ v4, c
 struct TpSplitWarp { // per-warp state (uniform unless noted)
     uint16_t *tstack;   // [D+1][M] level vectors
     uint32_t *va;       // [M/8][32][4] lane-private V, packed pairs, 16 bytes per lane per chunk
-    uint8_t *bstack;    // [TP_SPLIT_MAX_D] chosen B'' positions
+    uint8_t *bstack;    // [TP_SPLIT_MAX_D] chosen B'' positions; [8], [9]: the item's bounds on the second one
     u64 a0, a1;         // lane: A positions, one per byte, descending
     int active;         // lane: this lane holds a real A
     int lane;
@@ -489,7 +489,11 @@ struct TpSplitWalk {
                 if (w.lane == 0) w.bstack[L] = (uint8_t)b;
                 for (int wd = w.lane; wd < M / 2; wd += 32) dst[wd] = src[wd] + rw[wd];
                 __syncwarp();
-                TpSplitWalk<M, D, L + 1>::run(sh, s, w, P, b, sh.q - 2 - L, lb2, sb2, s_bound, best);
+                if constexpr (L == 0) // the item may hold only a sub-slice of the second position
+                    TpSplitWalk<M, D, 1>::run(sh, s, w, P, min(b, (int)w.bstack[9]), max(sh.q - 2, (int)w.bstack[8]), lb2,
+                                              sb2, s_bound, best);
+                else
+                    TpSplitWalk<M, D, L + 1>::run(sh, s, w, P, b, sh.q - 2 - L, lb2, sb2, s_bound, best);
             }
         } else {
             // leaf level: b is the last walked position, the pairs live below it
@@ -682,11 +686,13 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
     // the plan's per-pivot tables, block-shared (item -> pivot lookups happen once per item)
     __shared__ uint32_t s_item_base[TP_MAX_N], s_chunks[TP_MAX_N];
     __shared__ uint8_t s_pieces[TP_MAX_N];
+    __shared__ uint16_t s_cum[TP_MAX_N + 2];
     for (int i = threadIdx.x; i < plan->n_entries; i += blockDim.x) {
         s_item_base[i] = plan->item_base[i];
         s_chunks[i] = plan->n_chunks[i];
         s_pieces[i] = plan->n_pieces[i];
     }
+    for (int i = threadIdx.x; i < TP_MAX_N + 2; i += blockDim.x) s_cum[i] = plan->cum[i];
     __syncthreads();
     TpSplitShared sh{wp, wm, n, k, p, q, rq->dbits, rsp, plan->min_w};
     const int c_req = rq->c_req;
@@ -698,7 +704,11 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
         unsigned t_idx = 0;
         if (lane == 0) t_idx = atomicAdd(work_counter, 1u);
         t_idx = __shfl_sync(0xFFFFFFFFu, t_idx, 0);
-        const u64 item64 = (u64)t_idx * (unsigned)shard_cnt + (unsigned)shard_idx;
+        // Shard s of P owns item i when (i + i / P) mod P == s: the residue a shard takes rotates from
+        // one group of P items to the next, so no periodic pattern of the item list (slices of one
+        // pivot, chunks of one slice) lands on the same shard every time.
+        const unsigned rot = (unsigned)shard_idx + (unsigned)shard_cnt - t_idx % (unsigned)shard_cnt;
+        const u64 item64 = (u64)t_idx * (unsigned)shard_cnt + rot % (unsigned)shard_cnt;
         if (item64 >= total_items) break;
         const unsigned item = (unsigned)item64;
         // ---- item -> (pivot, chunk of A's, slice of the first B'' position) -----------------
@@ -715,15 +725,15 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
         const int jt = plan->jt_hi - e;
         const unsigned local = item - s_item_base[e];
         const unsigned nchunks = s_chunks[e];
-        const int piece = (int)(local / nchunks);
-        const unsigned ac = local - (unsigned)piece * nchunks;
-        int b0_lo = q - 1, b0_hi = jt;
+        const unsigned slice = local / nchunks;
+        const unsigned ac = local - slice * nchunks;
+        TpSlice sl{q - 1, jt, 0, TP_MAX_N, false};
         if (D > 0) {
-            const int np = s_pieces[e];
-            b0_lo = tp_split_cut(C, jt, q, np, piece);
-            b0_hi = tp_split_cut(C, jt, q, np, piece + 1);
-            if (b0_lo >= b0_hi) continue; // empty slice (one b0 value is the finest grain)
+            auto cum = [&](int b) -> int { return s_cum[b]; };
+            // (plan->b_star is read here, per item, rather than held in a register across the search)
+            if (!tp_split_slice(C, cum, jt, q, (int)s_pieces[e], plan->b_star, (int)slice, sl)) continue; // empty
         }
+        const int b0_lo = sl.b0_lo, b0_hi = sl.b0_hi;
 
         // ---- this lane's A: rank -> p-1 offsets above the pivot, colexicographic unrank --------
         // (largest first; the smallest offset varies fastest, so neighbouring lanes read
@@ -789,9 +799,15 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
         wst.a0 = a0;
         wst.a1 = a1;
         wst.active = active;
+        if (lane == 0) { // the item's bounds on the second walked position: read once per b0 by the walk
+            bstack[8] = (uint8_t)sl.b1_lo;
+            bstack[9] = (uint8_t)sl.b1_hi;
+        }
+        __syncwarp();
 
         u64 per_lane; // B sets this item scores per lane
         if (D == 0) per_lane = C(jt, 2);
+        else if (sl.cut_again) per_lane = C(sl.b1_hi, q - 1) - C(sl.b1_lo, q - 1);
         else per_lane = C(b0_hi, q) - C(b0_lo, q);
         if (lane == 0) counted += per_lane * (u64)min((u64)32, NA - (u64)ac * 32);
 
