@@ -241,3 +241,28 @@ def test_widest_topology_and_two_word_keys():
         assert pol.Decode(av, rq, k, min(keys)) == want
     assert tp.KERNEL_SPLIT in kernels and wide_keys > 0
     pol.close()
+
+
+@pytest.mark.parametrize("name", ["cpx", "missing", "hives"])
+def test_work_plan_with_cut_values(pols, name, monkeypatch):
+    """The work plan's second level: single values of the first walked position cut by the second one
+    (normally only for the heaviest values of large or sharded searches) is forced for every value by
+    the tuning knobs, at walk depths 2, 3 and 4; answers, scored counts and the min over shards must
+    not change."""
+    ref, pol = pols(name)
+    ids = [d.Id for d in ref.devices]
+    gen = topo.SplitMix64(0xC07 + len(ids))
+    monkeypatch.setenv("TP_SPLIT_CAP", "200")
+    monkeypatch.setenv("TP_SPLIT_CAP1", "150")
+    for size, cap in ((8, 30), (9, 26), (10, 24)):  # k' = size: D = 2, 3, 4
+        for _ in range(3):
+            pool = [i for i in ids if gen.chance(0.7)][:cap]
+            if len(pool) <= size + 2:
+                pool = ids[:size + 4]
+            want = ref.Allocate(pool, [], size)
+            got = pol.Allocate(pool, [], size)
+            assert got == want, (name, size, pool)
+            assert pol.last["kernel"] == tp.KERNEL_SPLIT and pol.last["score"] == ref.last["score"]
+            assert pol.last["subsets_scored"] == pol.last["subsets_total"]
+            keys = [pol.SearchShard(pool, [], size, s, 5) for s in range(5)]
+            assert pol.Decode(pool, [], size, min(keys)) == want
