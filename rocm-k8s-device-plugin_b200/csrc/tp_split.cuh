@@ -582,6 +582,41 @@ static __device__ __noinline__ void tp_split_family_seed(const TpSmem s, int n_g
     if (n_groups > TP_SEED_MAX_GROUPS) return;
     const unsigned n_masks = 1u << n_groups;
     int best = 0x7FFFFFFF;
+    if (n_masks <= blockDim.x) {
+        // Few groups (the usual node: 8 GPUs): one thread per mask would leave the few masks that
+        // carry members with all the scoring; spread (mask, partial group) pairs instead, at most
+        // one member per pair.  h == n_groups stands for "no partial group".
+        const unsigned per = (unsigned)n_groups + 1u;
+        for (unsigned unit = threadIdx.x; unit < n_masks * per; unit += blockDim.x) {
+            const unsigned mask = unit / per;
+            const int h = (int)(unit - mask * per);
+            if (h < n_groups && ((mask >> h) & 1u)) continue;
+            int pos[TP_MAX_K];
+            int cnt = 0;
+            bool over = false;
+            for (unsigned m = mask; m; m &= m - 1) {
+                const int g = __ffs(m) - 1;
+                const int gz = s.gsize[g], gs = s.gstart[g];
+                if (cnt + gz > k) {
+                    over = true;
+                    break;
+                }
+                for (int t = 0; t < gz; t++) pos[cnt++] = gs + t;
+            }
+            if (over) continue;
+            const int r = k - cnt;
+            if (h == n_groups ? r != 0 : (r == 0 || s.gsize[h] <= r)) continue;
+            for (int t = 0; t < r; t++) pos[cnt++] = s.gstart[h] + t; // the prefix (order does not matter here)
+            int sco = c_req;
+            for (int i = 0; i < cnt; i++) {
+                sco += s.u[pos[i]];
+                for (int j = 0; j < i; j++) sco += s.w[pos[j] * s.stride + pos[i]];
+            }
+            best = min(best, sco);
+        }
+        if (best != 0x7FFFFFFF) atomicMin(s_bound, best);
+        return;
+    }
     for (unsigned mask = threadIdx.x; mask < n_masks; mask += blockDim.x) {
         int pos[TP_MAX_K];
         int cnt = 0;
@@ -664,7 +699,8 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
             wm[j * Cfg::RS + jj] = (jj < j && jj < n) ? (uint16_t)src[-jj] : (uint16_t)TP_BIG;
     }
     for (int i = threadIdx.x; i < TP_MAX_N; i += blockDim.x) t0[i] = i < n ? s.u[n - 1 - i] : (uint16_t)0;
-    if (threadIdx.x == 0) { // second seed: whole groups from the largest down (also a Family member)
+    if (threadIdx.x == 0 && rq->n_groups > TP_SEED_MAX_GROUPS) { // second seed where the exact one does not run:
+        // whole groups from the largest down (also a Family member)
         int left = k, sco = rq->c_req, cnt = 0;
         int pos[TP_MAX_K];
         for (int g = rq->n_groups - 1; g >= 0 && left > 0; g--) {
