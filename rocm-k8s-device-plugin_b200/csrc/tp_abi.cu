@@ -869,16 +869,16 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         tp_policy::Batch &b = p->batch;
         size_t n_order = 0, plan_at = 0;
         std::vector<size_t> first(groups.size()), n_entries(groups.size());
+        std::vector<int> plan_slot(n_requests, -1); // where a request's plan goes in the pinned array
         for (size_t g = 0; g < groups.size(); g++) {
             BatchGroup &grp = groups[g];
             std::sort(grp.members.begin(), grp.members.end(),
                       [&](int x, int y) { return preps[x].rq.total > preps[y].rq.total; }); // heaviest first
             first[g] = n_order;
             for (int i : grp.members) {
-                b.h_reqs[i] = preps[i].rq;
                 int plan_idx = 0;
                 if (grp.kernel == TP_KERNEL_SPLIT) {
-                    b.h_plans[plan_at] = preps[i].plan;
+                    plan_slot[i] = (int)plan_at;
                     plan_idx = (int)plan_at++;
                 }
                 const int S = shares_of(i);
@@ -886,6 +886,21 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
                     b.h_order[n_order++] = TpBatchEntry{i, plan_idx, out_base[i] + sidx, (int16_t)sidx, (int16_t)S};
             }
             n_entries[g] = n_order - first[g];
+        }
+        { // descriptors and plans into the pinned arrays (~2.5 KB per request): worth a few threads
+            const unsigned hw = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+            const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_requests / 512 + 1));
+            auto work = [&](int t) {
+                for (int i = t; i < n_requests; i += nthreads) {
+                    if (out_base[i] < 0) continue; // not in a batch group
+                    b.h_reqs[i] = preps[i].rq;
+                    if (plan_slot[i] >= 0) b.h_plans[plan_slot[i]] = preps[i].plan;
+                }
+            };
+            std::vector<std::thread> pool;
+            for (int t = 1; t < nthreads; t++) pool.emplace_back(work, t);
+            work(0);
+            for (std::thread &t : pool) t.join();
         }
         const double t_stage = ms_since(t_start);
         TP_CUDA(p, cudaMemcpyAsync(b.d_reqs, b.h_reqs, (size_t)n_requests * sizeof(TpReq), cudaMemcpyHostToDevice, b.stream));

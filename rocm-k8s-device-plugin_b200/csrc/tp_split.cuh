@@ -770,6 +770,22 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
             if (!tp_split_slice(C, cum, jt, q, (int)s_pieces[e], plan->b_star, (int)slice, sl)) continue; // empty
         }
         const int b0_lo = sl.b0_lo, b0_hi = sl.b0_hi;
+        // Everything else the slice decides is settled here, so that only b0_lo / b0_hi stay live over
+        // the lane set-up below: the count of what the item scores, and the bounds on the second walked
+        // position, which the walk reads from the warp's byte area once per b0.  (All lanes left the
+        // previous item through a __syncwarp, nobody reads that area any more.)
+        {
+            u64 per_lane; // B sets this item scores per lane
+            if (D == 0) per_lane = C(jt, 2);
+            else if (sl.cut_again) per_lane = C(sl.b1_hi, q - 1) - C(sl.b1_lo, q - 1);
+            else per_lane = C(b0_hi, q) - C(b0_lo, q);
+            if (lane == 0) {
+                const u64 na = C(n - 1 - jt, p - 1);
+                counted += per_lane * (u64)min((u64)32, na - (u64)ac * 32);
+                bstack[8] = (uint8_t)sl.b1_lo;
+                bstack[9] = (uint8_t)sl.b1_hi;
+            }
+        }
 
         // ---- this lane's A: rank -> p-1 offsets above the pivot, colexicographic unrank --------
         // (largest first; the smallest offset varies fastest, so neighbouring lanes read
@@ -835,17 +851,6 @@ __device__ __noinline__ void tp_split_search(const uint8_t *__restrict__ W, int 
         wst.a0 = a0;
         wst.a1 = a1;
         wst.active = active;
-        if (lane == 0) { // the item's bounds on the second walked position: read once per b0 by the walk
-            bstack[8] = (uint8_t)sl.b1_lo;
-            bstack[9] = (uint8_t)sl.b1_hi;
-        }
-        __syncwarp();
-
-        u64 per_lane; // B sets this item scores per lane
-        if (D == 0) per_lane = C(jt, 2);
-        else if (sl.cut_again) per_lane = C(sl.b1_hi, q - 1) - C(sl.b1_lo, q - 1);
-        else per_lane = C(b0_hi, q) - C(b0_lo, q);
-        if (lane == 0) counted += per_lane * (u64)min((u64)32, NA - (u64)ac * 32);
 
         unsigned P[TP_SPLIT_PREGS];
         if constexpr (D == 0) {
