@@ -205,14 +205,15 @@ static __device__ void tp_stage_request(const TpSmem &s, const uint8_t *__restri
     for (int i = tid; i < n; i += nt) s_canon[i] = rq->canon[i];
     for (int a = warp; a <= n; a += nw)
         for (int j = lane; j <= K; j += 32) s.binom[a * (K + 1) + j] = binom_g[a * TP_BINOM_COLS + j];
-    if (n * n <= nt) { // tiny request (the latency path): one element per thread, no round trip through s_canon
-        if (tid < n * n) {
-            const int r = tid / n, c = tid - r * n;
+    const bool tiny = n <= 16; // the latency path (often a single warp): a flat loop, no round trip through s_canon
+    if (tiny) {
+        for (int i = tid; i < n * n; i += nt) {
+            const int r = i / n, c = i - r * n;
             s.w[r * s.stride + c] = (r == c) ? 0 : W[(int)rq->canon[r] * nd + rq->canon[c]];
         }
     }
     __syncthreads();
-    if (n * n > nt) {
+    if (!tiny) {
         for (int r = warp; r < n; r += nw) {
             const uint8_t *wrow = W + (int)s_canon[r] * nd;
             for (int c = lane; c < n; c += 32) s.w[r * s.stride + c] = (r == c) ? 0 : wrow[s_canon[c]];
