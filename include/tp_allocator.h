@@ -152,6 +152,14 @@ int tp_search_shard(tp_policy *p, const int32_t *available, int32_t n_available,
 int tp_decode(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
               int32_t n_required, int32_t size, const tp_key *key, int32_t *out);
 
+/* Host-only arithmetic of the sharding (works on a TP_DEVICE_NONE handle; no counterpart in the reference):
+ * how many subsets shard `shard_index` of `shard_count` scores for this request, and with which kernel.
+ * Over all shards the counts add up to C(free, size - n_required).  Returns 0, 1 for a request answered
+ * by a short-circuit (nothing to score), or a negative tp_status. */
+int tp_shard_subsets(tp_policy *p, const int32_t *available, int32_t n_available, const int32_t *required,
+                     int32_t n_required, int32_t size, int32_t shard_index, int32_t shard_count,
+                     uint64_t *subsets, int32_t *kernel);
+
 /* Measurement hook: the request is prepared and uploaded once, then the search
  * kernel is launched `iters` times back to back on the policy's stream between two
  * CUDA events; *ms receives the total device time.  No host<->device copy in the

@@ -115,6 +115,7 @@ def lib() -> C.CDLL:
                                     C.POINTER(TpResult)]
     L.tp_search_shard.argtypes = req_args + [C.c_int32, C.c_int32, C.POINTER(TpKey), C.POINTER(TpResult)]
     L.tp_decode.argtypes = req_args + [C.POINTER(TpKey), I32P]
+    L.tp_shard_subsets.argtypes = req_args + [C.c_int32, C.c_int32, C.POINTER(C.c_uint64), I32P]
     L.tp_search_resident.argtypes = req_args + [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_float),
                                                 C.POINTER(TpKey), C.POINTER(TpResult)]
     L.tp_build_weights.argtypes = [C.c_int32, I32P, I32P, I32P, C.POINTER(C.c_uint8), C.c_int32]
@@ -296,6 +297,17 @@ def search_resident(pol: BestEffortPolicy, available, required, size, iters=1, s
             msg += ": " + lib().tp_last_cuda_error(pol.handle).decode()
         raise AllocatorError(rc, msg)
     return ms.value, (key.hi, key.lo), res.dict()
+
+
+def shard_subsets(pol: BestEffortPolicy, available, required, size, shard_index, shard_count):
+    """tp_shard_subsets (host arithmetic only): (subsets this shard scores, kernel); None for a short-circuit."""
+    av, rq = pol.indices(available), pol.indices(required or [])
+    n, k = C.c_uint64(), C.c_int32()
+    rc = lib().tp_shard_subsets(pol.handle, _i32(av), len(av), _i32(rq), len(rq), size, shard_index, shard_count,
+                                C.byref(n), C.cast(C.byref(k), I32P))
+    if rc < 0:
+        raise AllocatorError(rc, strerror(rc))
+    return None if rc == 1 else (n.value, k.value)
 
 
 def allocate_indices(pol: BestEffortPolicy, av, rq, size):

@@ -1001,6 +1001,19 @@ int tp_search_shard(tp_policy *p, const int32_t *avail, int32_t n_avail, const i
     return 0;
 }
 
+int tp_shard_subsets(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req,
+                     int32_t size, int32_t shard_index, int32_t shard_count, uint64_t *subsets, int32_t *kernel) {
+    if (!p || !subsets || shard_count <= 0 || shard_index < 0 || shard_index >= shard_count) return TP_ERR_BAD_ARGUMENT;
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr, shard_count);
+    if (pr.status) return pr.status;
+    if (pr.shortcut) return 1;
+    if (pr.family_only) return TP_ERR_TOO_LARGE;
+    *subsets = shard_subsets(p, pr, shard_index, shard_count);
+    if (kernel) *kernel = pr.kernel;
+    return TP_OK;
+}
+
 int tp_decode(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req, int32_t size,
               const tp_key *key, int32_t *out) {
     if (!p || !key || !out) return TP_ERR_BAD_ARGUMENT;
