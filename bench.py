@@ -41,6 +41,23 @@ UNIT = "subsets/s"
 WORKLOAD = "C4: synthetic 10x8-partition topology (80 devices), GetPreferredAllocation 8 of 80, C(80,8)=28987537150 subsets/step"
 
 
+def bench_config(world):
+    """The `config` block, identical in both arms (the reference arm runs on the GPU arm's config)."""
+    return {"workload": WORKLOAD,
+            "sharding": f"subset space split x{world} (item stride), one min-exchange of the packed winner per step"
+            if world > 1 else "single GPU",
+            "l2": "flushed (256 MiB write) between timed steps"}
+
+
+def host_threads():
+    """Host threads the CPU arm may use: the affinity mask, not OMP_NUM_THREADS (torch.distributed.run
+    exports OMP_NUM_THREADS=1 to every rank, which would make the reference arm a 1-thread run)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def workload():
     import topo
     devs, pairs = topo.c4_topology()
@@ -101,14 +118,18 @@ def percentile(xs, p):
     return xs[min(len(xs) - 1, int(p / 100.0 * len(xs)))]
 
 
-def cpu_exhaustive(ref, ids, req, size, seconds, threads=0):
-    """Time oracle/exhaustive.c on ranks [0, X) of the workload, X sized for ~`seconds`."""
+def cpu_exhaustive(ref, ids, req, size, seconds, threads=0, rate=None):
+    """Time oracle/exhaustive.c on ranks [0, X) of the workload, X sized for ~`seconds` (the whole
+    space when it fits in that time)."""
     probe = 1 << 28
-    t = time.perf_counter()
-    ref.AllocateExhaustive(ids, req, size, threads=threads, rank_lo=0, rank_hi=probe)
-    dt = time.perf_counter() - t
-    rate = ref.last["scored"] / dt
-    sample = int(min(max(rate * seconds, probe), ref.last["total"]))
+    threads = threads or host_threads()
+    if rate is None:
+        t = time.perf_counter()
+        ref.AllocateExhaustive(ids, req, size, threads=threads, rank_lo=0, rank_hi=probe)
+        dt = time.perf_counter() - t
+        rate = ref.last["scored"] / dt
+    total = 28987537150
+    sample = int(min(max(rate * seconds, probe), total))
     t = time.perf_counter()
     ref.AllocateExhaustive(ids, req, size, threads=threads, rank_lo=0, rank_hi=sample)
     dt = time.perf_counter() - t
@@ -131,27 +152,31 @@ def run_reference(args, rank):
         lat.append((time.perf_counter() - t) * 1e6)
     assert out == expected and ref.last["score"] == score
     n_cand = ref.last["n_candidates"]
-    per_step_s = 4.0
-    for _ in range(args.warmup):
-        cpu_exhaustive(ref, ids, req, size, 0.5)
-    rates, scored, secs, threads = [], 0, 0.0, 1
+    # A step scores the whole C(80,8) when the host does that in <= 8 s (16 cores: ~3.8 s), else the
+    # first 8 s worth of ranks; warm-up steps are short (they only spin the OpenMP team up).
+    per_step_s = 8.0
+    rate = None
+    for _ in range(max(args.warmup, 1)):
+        rate, _, _, _ = cpu_exhaustive(ref, ids, req, size, 0.5)
+    scored, secs, threads = 0, 0.0, 1
     for _ in range(args.steps):
-        r, threads, n, dt = cpu_exhaustive(ref, ids, req, size, per_step_s)
-        rates.append(r)
+        r, threads, n, dt = cpu_exhaustive(ref, ids, req, size, per_step_s, rate=rate)
         scored += n
         secs += dt
     value = scored / secs
-    sample = f"ranks [0, ~{scored // max(args.steps, 1)}) of C(80,8) per step, oracle/exhaustive.c"
+    per_step = scored // max(args.steps, 1)
+    sample = (f"{'all' if per_step == 28987537150 else 'ranks [0, ' + str(per_step) + ') of the'} "
+              f"28987537150 subsets of C(80,8) per step, oracle/exhaustive.c, {threads} OpenMP threads")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(args.steps, 1) * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int32",
-            "data": "synthetic", "config": {"workload": WORKLOAD, "note": "bounded sample per step"},
+            "data": "synthetic", "config": bench_config(args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "reference_policy": {"what": "BFS restatement of BestEffortPolicy.Allocate (oracle/ref_policy.c), 1 thread",
                                  "candidates_scored": n_cand, "p50_us": percentile(lat, 50),
                                  "p99_us": percentile(lat, 99)},
-            "host_cores": os.cpu_count()}
+            "host_cores": os.cpu_count(), "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS")}
     print(json.dumps(line))
 
 
@@ -307,21 +332,28 @@ def main():
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None,
                 "dtype": "u16" if info["kernel"] == tp.KERNEL_SPLIT else "int32", "data": "synthetic",
-                "config": {"workload": WORKLOAD, "sharding": f"subset space split x{world} (item stride), one NCCL min all-reduce/step"
-                           if world > 1 else "single GPU", "l2": "flushed (256 MiB write) between timed steps",
-                           "kernel": {1: "lex", 2: "split"}.get(info["kernel"], str(info["kernel"]))},
+                "config": bench_config(world),
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": e2e_s / args.steps * 1e3, "api": "BestEffortPolicy.Allocate(ids, req, size)"},
                 "gpu_launches": launches, "roofline": roofline}
         if world == 1 and not args.no_extra:
             line["latency"] = latency_leg(tp, dev)
-            line["c3"] = c3_leg(tp)
+            line["c3"] = c3_leg(tp, peak_addmin)
             line["c5_pod_storm"] = pod_storm_leg(tp)
         if world == 1 and not args.no_cpu:
             from oracle.binding import RefPolicy
             ref = RefPolicy()
             ref.InitPairs(devs, pairs)
+            lat = []
+            for _ in range(200):  # the reference's own algorithm on this request, beside the exhaustive numbers
+                t = time.perf_counter()
+                ref.Allocate(ids, req, size)
+                lat.append((time.perf_counter() - t) * 1e6)
+            line["reference_policy"] = {"what": "BFS restatement of BestEffortPolicy.Allocate (oracle/ref_policy.c), 1 thread, "
+                                                "same request; the exhaustive search returns the same ids",
+                                        "candidates_scored": ref.last["n_candidates"], "p50_us": percentile(lat, 50),
+                                        "p99_us": percentile(lat, 99)}
             r, threads, n, dt = cpu_exhaustive(ref, ids, req, size, 12.0)
             line["cpu_baseline"] = {"value": r, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"ranks [0, {n}) of C(80,8) in {dt:.1f}s, oracle/exhaustive.c, "
@@ -444,8 +476,10 @@ def pod_storm_leg(tp, count=10000):
                     "cpu column = oracle BFS restatement, 1 thread, python call overhead included"}
 
 
-def c3_leg(tp):
-    """BASELINE config C3: CPX fixture 8 of 63 (parity case) and 8 of 64 (the ~4.4e9 figure)."""
+def c3_leg(tp, peak_addmin):
+    """BASELINE config C3: CPX fixture 8 of 63 (parity case) and 8 of 64 (the ~4.4e9 figure), each with the
+    same roofline arithmetic as the headline kernel (2 sixteen-bit ops per subset against the measured
+    VIADDMNMX.U16x2 rate x 4)."""
     import topo
     res = {}
     for name, (devs, pairs), first in (("cpx_8of63", topo.fixture_topology("cpx"), "test1"),
@@ -453,12 +487,17 @@ def c3_leg(tp):
         ids = [d.Id for d in devs]
         pol = tp.BestEffortPolicy(cuda_device=0)
         pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
-        tp.search_resident(pol, ids, [], 8, iters=1)
-        ms, key, info = tp.search_resident(pol, ids, [], 8, iters=5)
+        tp.search_resident(pol, ids, [], 8, iters=3)
+        ms, key, info = tp.search_resident(pol, ids, [], 8, iters=20)
         got = pol.Decode(ids, [], 8, key)
         assert got[0] == first and info["score"] == 840, (got, info)
-        res[name] = {"subsets": info["subsets_total"], "kernel_ms": ms / 5,
-                     "subsets_per_s": info["subsets_total"] / (ms / 5 * 1e-3), "winner": got}
+        rate = info["subsets_total"] / (ms / 20 * 1e-3)
+        achieved, peak = rate * 2 / 1e12, peak_addmin * 4 / 1e3
+        res[name] = {"subsets": info["subsets_total"], "kernel_ms": ms / 20, "subsets_per_s": rate, "winner": got,
+                     "roofline": {"bound": "int-alu", "achieved": achieved, "peak": peak, "unit": "Tops/s",
+                                  "frac": achieved / peak, "ops_per_subset": 2,
+                                  "kernel": tp.kernel_name(info["kernel"]),
+                                  "peak_source": "VIADDMNMX.U16x2 microbenchmark in this run x 4 ops/lane-instr"}}
         pol.close()
     return res
 
