@@ -211,6 +211,13 @@ int tp_allocate_static(const tp_topology *topo, const uint8_t *d_weight, const i
                        int32_t n_available, const int32_t *required, int32_t n_required, int32_t size,
                        void *cuda_stream, uint64_t *d_out, int32_t *out, tp_result *info);
 
+/* Development hook (tests, tuning sweeps; no counterpart in the reference): override the work plan of the
+ * exhaustive kernels for requests prepared after the call -- walk_q = positions below the lane set (forces
+ * kernel SPLIT), item_cap / item_cap1 = subsets per lane per work item / per cut value; 0 = default.  The
+ * same three values are read ONCE, in tp_create, from the environment variables TP_SPLIT_Q, TP_SPLIT_CAP and
+ * TP_SPLIT_CAP1; nothing on the request path reads the environment.  Not thread-safe against running calls. */
+void tp_set_tuning(tp_policy *p, int32_t walk_q, uint64_t item_cap, uint64_t item_cap1);
+
 /* Roofline denominator: dependency-free integer-ALU microbenchmark on the given device.
  * variant 0: IADD3 only (alu pipe); 1: IADD3 + IMAD mix (alu + fma pipes); 2: packed
  * 16x2 min (VIMNMX).  *gops receives 10^9 lane-operations per second. */

@@ -27,9 +27,13 @@ STATUS = {
     "TP_OK": 0, "TP_ERR_INVALID_SIZE": -1, "TP_ERR_INVALID_AVAILABLE": -2, "TP_ERR_INVALID_REQUIRED": -3,
     "TP_ERR_INVALID_REQ_AVAILABLE": -4, "TP_ERR_INVALID_INIT": -5, "TP_ERR_NO_CANDIDATE": -6,
     "TP_ERR_INIT_FAILED": -7, "TP_ERR_BAD_INDEX": -20, "TP_ERR_BAD_ARGUMENT": -21, "TP_ERR_TOO_LARGE": -22,
-    "TP_ERR_CUDA": -30, "TP_ERR_NCCL": -31,
+    "TP_ERR_STATIC_SCRATCH": -23, "TP_ERR_CUDA": -30, "TP_ERR_NCCL": -31,
 }
-KERNEL_AUTO, KERNEL_LEX, KERNEL_SPLIT, KERNEL_FAMILY = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_LEX, KERNEL_SPLIT, KERNEL_FAMILY, KERNEL_TRI = 0, 1, 2, 3, 4
+
+
+def kernel_name(kernel: int) -> str:
+    return {1: "lex", 2: "split", 3: "family", 4: "tri"}.get(kernel, str(kernel))
 
 
 class TpKey(C.Structure):
@@ -126,6 +130,8 @@ def lib() -> C.CDLL:
     L.tp_prepared_free.argtypes = [C.c_void_p, C.c_void_p]
     L.tp_prepared_free.restype = None
     L.tp_measure_int_peak.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_double)]
+    L.tp_set_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64]
+    L.tp_set_tuning.restype = None
     L.tp_allocate_static.argtypes = [C.POINTER(TpTopology), C.c_void_p, I32P, C.c_int32, I32P, C.c_int32,
                                      C.c_int32, C.c_void_p, C.c_void_p, I32P, C.POINTER(TpResult)]
     L.tph_new.restype = C.c_void_p
@@ -223,6 +229,10 @@ class BestEffortPolicy:
         if rc < 0:
             self._raise(rc)
         return _ids(out, rc)
+
+    def set_tuning(self, walk_q=0, item_cap=0, item_cap1=0):
+        """tp_set_tuning (development hook): override the work plan of requests prepared from now on."""
+        lib().tp_set_tuning(self.handle, walk_q, item_cap, item_cap1)
 
     def GlobalOptimum(self, available, required, size):
         """tp_global_optimum: the best set over ALL subsets (advisory; not what the reference returns)."""

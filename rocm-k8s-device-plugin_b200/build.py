@@ -13,14 +13,18 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
-OBJ = os.path.join(HERE, "build")
-LIB = os.path.join(HERE, "libtpalloc.so")
+# A/B builds (tuning aid): TP_BUILD_TAG=x TP_BUILD_DEFS="-DTP_TRI_GT=12" python build.py -> libtpalloc_x.so, to be
+# loaded with TP_ALLOC_LIB=<path>; the default build has no tag.
+TAG = os.environ.get("TP_BUILD_TAG", "")
+OBJ = os.path.join("/tmp", "tpalloc_build_" + TAG) if TAG else os.path.join(HERE, "build")  # (tagged objects stay out of the tree)
+LIB = os.path.join(HERE, "libtpalloc" + ("_" + TAG if TAG else "") + ".so")
 SPLIT_UNITS = [f"csrc/tp_split_m{m}_d{d}.cu" for m in (128, 96, 80, 64) for d in (4, 3, 2, 1, 0)]  # slowest first
-SOURCES = SPLIT_UNITS + ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
-HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_device.cuh", "csrc/tp_split.cuh",
+TRI_UNITS = [f"csrc/tp_tri_m{m}_d{d}.cu" for m in (80, 64) for d in (3, 2, 1, 0)]
+SOURCES = TRI_UNITS + SPLIT_UNITS + ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
+HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_device.cuh", "csrc/tp_split.cuh", "csrc/tp_tri.cuh",
            "host/besteffort_policy.h"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall"] + ARCH
+CFLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-O3,-Wall"] + ARCH + os.environ.get("TP_BUILD_DEFS", "").split()
 INCLUDES = ["-I", os.path.join(ROOT, "include"), "-I", CSRC]
 
 

@@ -62,7 +62,9 @@ struct Prep {
     bool batch = false;       // prepared for tp_allocate_batch: a block, not the grid, takes each share
 };
 
-// tp_allocate_batch cuts a heavy SPLIT request into this many shares, each taken by one block.
+inline bool uses_plan(int kernel) { return kernel == TP_KERNEL_SPLIT || kernel == TP_KERNEL_TRI; }
+
+// tp_allocate_batch cuts a heavy SPLIT / TRI request into this many shares, each taken by one block.
 inline int batch_shares(u64 total) { return total <= (1ull << 24) ? 1 : (int)std::min<u64>(16, (total >> 24) + 1); }
 
 } // namespace
@@ -76,6 +78,11 @@ struct tp_policy {
     int cuda_device = 0, sm_count = 148;
     int kernel = 0;
     u64 exhaustive_limit = 0;
+    // development knobs, read from the environment ONCE in tp_create (never on the request path):
+    // TP_SPLIT_Q (walk split), TP_SPLIT_CAP / TP_SPLIT_CAP1 (item sizes), TP_BATCH_TRACE (phase timings)
+    int tune_q = 0;
+    u64 tune_cap = 0, tune_cap1 = 0;
+    bool batch_trace = false;
     uint8_t *d_weight = nullptr;
     u64 *d_binom = nullptr;
     u64 binom[TP_MAX_N + 1][TP_BINOM_COLS];
@@ -192,16 +199,24 @@ void free_ctx(Ctx &c) {
     if (c.d_scratch) cudaFree(c.d_scratch);
 }
 
-// Work plan of kernel SPLIT for a prepared request (out.rq filled).  Returns false when the
-// request is outside what that kernel takes (k' < 4, too many positions per lane, scores that
-// would not fit its 16-bit packed arithmetic); the LEX kernel then serves it.
+// Work plan of kernels SPLIT and TRI for a prepared request (out.rq filled): sets out.kernel.
+// Returns false when the request is outside what those kernels take (k' < 4, too many positions
+// per lane, scores that would not fit their 16-bit packed arithmetic); the LEX kernel then serves it.
+// TRI (three positions against the triple table) takes k' >= 6 on n - p <= 80 positions; SPLIT the rest.
 bool build_plan(const tp_policy *p, Prep &out) {
     const TpReq &rq = out.rq;
     const int n = rq.n, k = rq.k;
     if (k < 4 || k > TP_MAX_K) return false;
     int q = k >= 6 ? std::min(k - 4, TP_SPLIT_MAX_D + 2) : 2;
-    if (const char *env = getenv("TP_SPLIT_Q")) q = std::max(2, std::min({atoi(env), k - 1, TP_SPLIT_MAX_D + 2})); // tuning aid
-    const int pp = k - q;
+    if (p->tune_q) q = std::max(2, std::min({p->tune_q, k - 1, TP_SPLIT_MAX_D + 2})); // tuning aid
+    int pp = k - q, tri_gcap = 0;
+    if (k >= 6 && p->kernel != TP_KERNEL_SPLIT && !p->tune_q) {
+        const int tq = std::max(3, std::min(k - 4, TP_TRI_MAX_DW + 3)), tpp = k - tq;
+        if (tpp <= TP_SPLIT_MAX_P && n - tpp >= tq && (tri_gcap = tp_tri_fit(n, k, tpp, tq)) > 0) {
+            q = tq;
+            pp = tpp;
+        }
+    }
     if (pp > TP_SPLIT_MAX_P || n - pp > TP_SPLIT_MAX_M || n - pp < q) return false;
     int max_w = 0, max_u = 0, min_w = 255;
     for (int i = 0; i < n; i++) {
@@ -233,7 +248,7 @@ bool build_plan(const tp_policy *p, Prep &out) {
     // them, and larger items spend less on the per-item set-up (unrank, lane vectors).
     if (out.batch)
         cap0 = std::min<u64>(std::max<u64>(2048, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 6)), 65536);
-    if (const char *env = getenv("TP_SPLIT_CAP")) cap0 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
+    if (p->tune_cap) cap0 = std::max<u64>(64, p->tune_cap); // tuning aid
     // Single values of b0 become items of their own, cut by b1 (D >= 2 only) -- only where it matters:
     // when one value alone is more than a quarter of what a lane has to do in this search (shard);
     // restricted b1 ranges lose the compile-time leaf blocks and add per-item set-up.
@@ -242,7 +257,7 @@ bool build_plan(const tp_policy *p, Prep &out) {
         const u64 lanes = (u64)p->sm_count * 2 * TP_SPLIT_THREADS;
         u64 cap1 = std::max<u64>(cap0, rq.total / (lanes * (u64)std::max(out.shards, 1) * 4));
         if (out.batch) cap1 = std::max<u64>(cap0, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 4));
-        if (const char *env = getenv("TP_SPLIT_CAP1")) cap1 = std::max<u64>(64, strtoull(env, nullptr, 10)); // tuning aid
+        if (p->tune_cap1) cap1 = std::max<u64>(64, p->tune_cap1); // tuning aid
         int bs = q - 1;
         while (bs < n && p->binom[bs][q - 1] <= cap1) bs++;
         pl.b_star = bs;
@@ -269,6 +284,8 @@ bool build_plan(const tp_policy *p, Prep &out) {
         if (items > 0xFFFFFFF0ull) return false;
     }
     pl.total_items = (uint32_t)items;
+    pl.tri_gcap = tri_gcap;
+    out.kernel = tri_gcap > 0 ? TP_KERNEL_TRI : TP_KERNEL_SPLIT;
     return true;
 }
 
@@ -367,7 +384,7 @@ void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_
         return;
     }
     if (p->kernel == TP_KERNEL_AUTO && rq.total <= TP_FAST_MAX_SUBSETS) return; // small: LEX (latency path), no plan
-    if (!out.family_only && p->kernel != TP_KERNEL_LEX && build_plan(p, out)) out.kernel = TP_KERNEL_SPLIT;
+    if (!out.family_only && p->kernel != TP_KERNEL_LEX) build_plan(p, out); // sets out.kernel on success
 }
 
 // Advisory mode (tp_global_optimum): every free device becomes a group of its own, so Family holds
@@ -390,7 +407,7 @@ int ungroup(const tp_policy *p, Prep &pr) {
     pr.family_masks = 0;
     pr.kernel = TP_KERNEL_LEX;
     if (p->kernel == TP_KERNEL_AUTO && rq.total <= TP_FAST_MAX_SUBSETS) return 0;
-    if (p->kernel != TP_KERNEL_LEX && build_plan(p, pr)) pr.kernel = TP_KERNEL_SPLIT;
+    if (p->kernel != TP_KERNEL_LEX) build_plan(p, pr);
     return 0;
 }
 
@@ -422,7 +439,7 @@ void shard_range(u64 total, int idx, int cnt, u64 &lo, u64 &hi) {
 cudaError_t upload_request(Ctx &c, const Prep &pr) {
     *c.h_req = pr.rq;
     size_t bytes = sizeof(TpReq);
-    if (pr.kernel == TP_KERNEL_SPLIT) {
+    if (uses_plan(pr.kernel)) {
         *c.h_plan = pr.plan;
         bytes += sizeof(TpPlan);
     }
@@ -431,7 +448,7 @@ cudaError_t upload_request(Ctx &c, const Prep &pr) {
 
 // Does shard (idx of cnt) hold any work?  LEX shards by rank range, SPLIT by rotating item stride.
 bool shard_nonempty(const Prep &pr, int idx, int cnt) {
-    if (pr.kernel == TP_KERNEL_SPLIT) return (u64)idx < pr.plan.total_items;
+    if (uses_plan(pr.kernel)) return (u64)idx < pr.plan.total_items;
     u64 lo, hi;
     shard_range(pr.kernel == TP_KERNEL_FAMILY ? pr.family_masks : pr.rq.total, idx, cnt, lo, hi);
     return hi > lo;
@@ -440,7 +457,7 @@ bool shard_nonempty(const Prep &pr, int idx, int cnt) {
 // Subsets shard (idx of cnt) scores in one launch.
 u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
     if (pr.kernel == TP_KERNEL_FAMILY) return 0; // Family members are counted by the kernel only
-    if (pr.kernel != TP_KERNEL_SPLIT) {
+    if (!uses_plan(pr.kernel)) {
         u64 lo, hi;
         shard_range(pr.rq.total, idx, cnt, lo, hi);
         return hi - lo;
@@ -477,6 +494,9 @@ u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
 // Enqueue the search kernel chosen by prepare() for shard (idx of cnt) on `st`, result into sc.out.
 cudaError_t launch_search(tp_policy *p, Ctx &c, const Prep &pr, int idx, int cnt, const TpScratch &sc,
                           cudaStream_t st, TpLaunchInfo *li) {
+    if (pr.kernel == TP_KERNEL_TRI)
+        return tp_launch_exhaustive_tri(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, c.d_plan, pr.plan, idx, cnt, sc,
+                                        c.d_counter, p->sm_count, st, li);
     if (pr.kernel == TP_KERNEL_SPLIT)
         return tp_launch_exhaustive_split(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, c.d_plan, pr.plan, idx, cnt,
                                           sc, c.d_counter, p->sm_count, st, li);
@@ -633,6 +653,10 @@ int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
         }
     p->kernel = o ? o->kernel : 0;
     p->exhaustive_limit = o ? o->exhaustive_limit : 0;
+    if (const char *env = getenv("TP_SPLIT_Q")) p->tune_q = atoi(env);
+    if (const char *env = getenv("TP_SPLIT_CAP")) p->tune_cap = strtoull(env, nullptr, 10);
+    if (const char *env = getenv("TP_SPLIT_CAP1")) p->tune_cap1 = strtoull(env, nullptr, 10);
+    p->batch_trace = getenv("TP_BATCH_TRACE") != nullptr;
     int dev = o ? o->cuda_device : -1;
     if (dev == TP_DEVICE_NONE) { // host-only handle: validation, sharding arithmetic and tp_decode work,
         p->host_only = true;     // every entry point that would search returns TP_ERR_CUDA
@@ -769,8 +793,8 @@ int batch_reserve(tp_policy *p, size_t n_reqs, size_t n_plans) {
 }
 
 struct BatchGroup {
-    int kernel, a, b, c; // LEX: (k', -, -); SPLIT: (p, q, lane-vector class)
-    int max_n = 0, max_k = 0;
+    int kernel, a, b, c; // LEX: (k', -, -); SPLIT / TRI: (p, q, lane-vector class)
+    int max_n = 0, max_k = 0, max_gcap = 0;
     std::vector<int> members; // request indices
 };
 
@@ -792,7 +816,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         }
         return TP_OK;
     }
-    const bool trace = getenv("TP_BATCH_TRACE") != nullptr; // phase timings on stderr (tuning aid)
+    const bool trace = p->batch_trace; // phase timings on stderr (tuning aid)
     auto now = [] { return std::chrono::steady_clock::now(); };
     auto ms_since = [&](std::chrono::steady_clock::time_point t0) {
         return std::chrono::duration<double, std::milli>(now() - t0).count();
@@ -830,7 +854,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         if (pr.family_only || pr.kernel == TP_KERNEL_FAMILY) { singles.push_back(i); continue; }
         BatchGroup key;
         key.kernel = pr.kernel;
-        if (pr.kernel == TP_KERNEL_SPLIT) {
+        if (uses_plan(pr.kernel)) {
             const int need = pr.rq.n - pr.plan.p;
             key.a = pr.plan.p; key.b = pr.plan.q; key.c = need <= 64 ? 64 : need <= 80 ? 80 : need <= 96 ? 96 : 128;
             n_plans++;
@@ -841,12 +865,13 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         for (; g < groups.size(); g++)
             if (groups[g].kernel == key.kernel && groups[g].a == key.a && groups[g].b == key.b && groups[g].c == key.c) break;
         if (g == groups.size()) {
-            if ((int)groups.size() == kBatchMaxGroups) { singles.push_back(i); if (pr.kernel == TP_KERNEL_SPLIT) n_plans--; continue; }
+            if ((int)groups.size() == kBatchMaxGroups) { singles.push_back(i); if (uses_plan(pr.kernel)) n_plans--; continue; }
             groups.push_back(key);
         }
         groups[g].members.push_back(i);
         groups[g].max_n = std::max(groups[g].max_n, pr.rq.n);
         groups[g].max_k = std::max(groups[g].max_k, pr.rq.k);
+        if (pr.kernel == TP_KERNEL_TRI) groups[g].max_gcap = std::max(groups[g].max_gcap, (int)pr.plan.tri_gcap);
     }
     int launches = 0;
     if (!groups.empty()) {
@@ -855,7 +880,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         // Heavy requests are cut into shares taken by different blocks (the same item striding as
         // multi-GPU shards), so that one big search does not become the tail of its group.
         auto shares_of = [&](int i) -> int {
-            return preps[i].kernel == TP_KERNEL_SPLIT ? batch_shares(preps[i].rq.total) : 1;
+            return uses_plan(preps[i].kernel) ? batch_shares(preps[i].rq.total) : 1;
         };
         size_t n_out = 0;
         std::vector<int> out_base(n_requests, -1);
@@ -877,7 +902,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
             first[g] = n_order;
             for (int i : grp.members) {
                 int plan_idx = 0;
-                if (grp.kernel == TP_KERNEL_SPLIT) {
+                if (uses_plan(grp.kernel)) {
                     plan_slot[i] = (int)plan_at;
                     plan_idx = (int)plan_at++;
                 }
@@ -911,7 +936,10 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
             const BatchGroup &grp = groups[g];
             TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + g, (int32_t)n_entries[g], 0};
             TpLaunchInfo li{};
-            if (grp.kernel == TP_KERNEL_SPLIT)
+            if (grp.kernel == TP_KERNEL_TRI)
+                TP_CUDA(p, tp_launch_batch_tri(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
+                                               grp.max_n, grp.max_k, grp.max_gcap, tb, p->sm_count, b.stream, &li));
+            else if (grp.kernel == TP_KERNEL_SPLIT)
                 TP_CUDA(p, tp_launch_batch_split(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
                                                  grp.max_n, grp.max_k, tb, p->sm_count, b.stream, &li));
             else
@@ -1163,6 +1191,13 @@ int tp_allocate_static(const tp_topology *t, const uint8_t *d_weight, const int3
         }
     }
     return decode(pr, key, req, out);
+}
+
+void tp_set_tuning(tp_policy *p, int32_t walk_q, uint64_t item_cap, uint64_t item_cap1) {
+    if (!p) return;
+    p->tune_q = walk_q;
+    p->tune_cap = item_cap;
+    p->tune_cap1 = item_cap1;
 }
 
 int tp_measure_int_peak(int32_t cuda_device, int32_t variant, double *gops) {

@@ -146,6 +146,7 @@ struct TpPlan {
     uint8_t n_pieces[TP_MAX_N];   // slices of the first walked position below b_star, see tp_split_cut
     int32_t b_star;               // values b0 >= b_star are items of their own, cut again (see cum)
     uint16_t cum[TP_MAX_N + 2];   // cum[b] = sub-slices of the single values b_star .. b-1
+    int32_t tri_gcap;             // kernel TRI: leaf pairs (leaves 2g+1, 2g+2) that have a table in shared memory
 };
 #define TP_SPLIT_MAX_SUB 16
 

@@ -457,6 +457,74 @@ cudaError_t tp_launch_batch_split(const uint8_t *d_weight, int n_devices, const 
                              nullptr, sm_count, st, info, batch);
 }
 
+// Kernel TRI: lane vectors of 64 or 80 positions, 0..3 walked positions above the triple.
+#define TP_TRI_MAX_DYN_SMEM (232448 - 6144) /* 227 KB per block minus the kernel's static shared memory */
+static size_t tp_tri_smem(int need, int DW, int n, int k, int gcap) {
+#define TP_TRI_SMEM_BY_DEPTH(M)                          \
+    switch (DW) {                                        \
+    case 0: return tp_tri_smem_m##M##_d0(n, k, gcap);    \
+    case 1: return tp_tri_smem_m##M##_d1(n, k, gcap);    \
+    case 2: return tp_tri_smem_m##M##_d2(n, k, gcap);    \
+    case 3: return tp_tri_smem_m##M##_d3(n, k, gcap);    \
+    default: return ~(size_t)0;                          \
+    }
+    if (need <= 64) { TP_TRI_SMEM_BY_DEPTH(64) }
+    if (need <= 80) { TP_TRI_SMEM_BY_DEPTH(80) }
+#undef TP_TRI_SMEM_BY_DEPTH
+    return ~(size_t)0;
+}
+
+int tp_tri_fit(int n, int k, int p, int q) {
+    const int DW = q - 3, need = n - p;
+    if (DW < 0 || DW > TP_TRI_MAX_DW || need > TP_TRI_MAX_M || p < 1) return 0;
+    // the top of the triple reaches need - 1 - DW; leaf b belongs to pair (b - 1) / 2
+    int gcap = (need - 1 - DW - 1) / 2 + 1;
+    if (gcap > tp_tri_gc()) gcap = tp_tri_gc(); // the lane registers hold 2 TP_TRI_GC positions
+    while (gcap >= 4 && tp_tri_smem(need, DW, n, k, gcap) > TP_TRI_MAX_DYN_SMEM) gcap--;
+    return gcap >= 4 ? gcap : 0;
+}
+
+static cudaError_t tp_dispatch_tri(int DW, int need, const uint8_t *d_weight, int n_devices, const u64 *d_binom,
+                                   const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int gcap, int shard_idx,
+                                   int shard_cnt, const TpScratch &sc, unsigned *d_counter, int sm_count,
+                                   cudaStream_t st, TpLaunchInfo *info, const TpBatch &batch) {
+#define TP_TRI_ARGS \
+    d_weight, n_devices, d_binom, d_rq, h, d_plan, gcap, shard_idx, shard_cnt, sc, d_counter, sm_count, st, info, batch
+#define TP_TRI_BY_DEPTH(M)                                 \
+    switch (DW) {                                          \
+    case 0: return tp_launch_tri_m##M##_d0(TP_TRI_ARGS);   \
+    case 1: return tp_launch_tri_m##M##_d1(TP_TRI_ARGS);   \
+    case 2: return tp_launch_tri_m##M##_d2(TP_TRI_ARGS);   \
+    case 3: return tp_launch_tri_m##M##_d3(TP_TRI_ARGS);   \
+    default: return cudaErrorInvalidValue;                 \
+    }
+    if (need <= 64) { TP_TRI_BY_DEPTH(64) }
+    if (need <= 80) { TP_TRI_BY_DEPTH(80) }
+#undef TP_TRI_BY_DEPTH
+#undef TP_TRI_ARGS
+    return cudaErrorInvalidValue;
+}
+
+cudaError_t tp_launch_exhaustive_tri(const uint8_t *d_weight, int n_devices, const u64 *d_binom, const TpReq *d_rq,
+                                     const TpReq &h, const TpPlan *d_plan, const TpPlan &hp, int shard_idx,
+                                     int shard_cnt, const TpScratch &sc, unsigned *d_counter, int sm_count,
+                                     cudaStream_t st, TpLaunchInfo *info) {
+    TpBatch single{};
+    return tp_dispatch_tri(hp.q - 3, h.n - hp.p, d_weight, n_devices, d_binom, d_rq, h, d_plan, hp.tri_gcap,
+                           shard_idx, shard_cnt, sc, d_counter, sm_count, st, info, single);
+}
+
+cudaError_t tp_launch_batch_tri(const uint8_t *d_weight, int n_devices, const u64 *d_binom, const TpReq *d_reqs,
+                                const TpPlan *d_plans, int p, int q, int max_n, int max_k, int max_gcap,
+                                const TpBatch &batch, int sm_count, cudaStream_t st, TpLaunchInfo *info) {
+    TpReq h{};
+    h.n = max_n; // sizes the shared memory for the largest request of the group
+    h.k = max_k;
+    TpScratch none{};
+    return tp_dispatch_tri(q - 3, max_n - p, d_weight, n_devices, d_binom, d_reqs, h, d_plans, max_gcap, 0, 1, none,
+                           nullptr, sm_count, st, info, batch);
+}
+
 // ---------------------------------------------------------------------------------------
 // calculatePairWeight (device.go:135-157) for every pair at once.
 // ---------------------------------------------------------------------------------------

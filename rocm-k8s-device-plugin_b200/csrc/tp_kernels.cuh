@@ -7,6 +7,7 @@ enum TpKernelId {
     TP_KERNEL_LEX = 1,    // tp_exhaustive_lex: one rank range per thread, lexicographic walk
     TP_KERNEL_SPLIT = 2,  // tp_exhaustive_split: lane sets x warp-uniform walk x unrolled pair nest
     TP_KERNEL_FAMILY = 3, // tp_family: Family members only (search spaces too large to enumerate)
+    TP_KERNEL_TRI = 4,    // tp_exhaustive_tri: lane sets x warp-uniform walk x triple table (k' >= 6, n - p <= 80)
 };
 
 struct TpLaunchInfo {
@@ -43,6 +44,33 @@ TP_DECLARE_SPLIT_LAUNCHERS(64)
 TP_DECLARE_SPLIT_LAUNCHERS(80)
 TP_DECLARE_SPLIT_LAUNCHERS(96)
 TP_DECLARE_SPLIT_LAUNCHERS(128)
+
+// Kernel TRI (tp_tri.cuh): same plan, shards and scratch as SPLIT; needs n - plan.p <= TP_TRI_MAX_M, plan.q in
+// [3, 6] and plan.tri_gcap from tp_tri_fit.
+#define TP_TRI_MAX_M 80
+#define TP_TRI_MAX_DW 3
+cudaError_t tp_launch_exhaustive_tri(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                     const TpReq *d_rq, const TpReq &h_rq, const TpPlan *d_plan,
+                                     const TpPlan &h_plan, int shard_idx, int shard_cnt, const TpScratch &scratch,
+                                     unsigned *d_counter, int sm_count, cudaStream_t stream, TpLaunchInfo *info);
+cudaError_t tp_launch_batch_tri(const uint8_t *d_weight, int n_devices, const unsigned long long *d_binom,
+                                const TpReq *d_reqs, const TpPlan *d_plans, int p, int q, int max_n, int max_k,
+                                int max_gcap, const TpBatch &batch, int sm_count, cudaStream_t stream,
+                                TpLaunchInfo *info);
+// Largest table cap (leaf pairs) whose shared memory fits beside everything else the kernel stages for a
+// request with n free devices, k' = k, |A| = p and q positions below the lane set; 0 = kernel TRI cannot run.
+int tp_tri_fit(int n, int k, int p, int q);
+int tp_tri_gc(); // TP_TRI_GC of the build (defined next to the kernel, tp_tri_m64_d0.cu)
+#define TP_DECLARE_TRI_LAUNCHER(M, D)                                                                            \
+    cudaError_t tp_launch_tri_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,            \
+                                          const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int gcap,    \
+                                          int si, int sn, const TpScratch &sc, unsigned *d_counter, int sms,    \
+                                          cudaStream_t st, TpLaunchInfo *info, const TpBatch &batch);           \
+    size_t tp_tri_smem_m##M##_d##D(int n, int k, int gcap);
+#define TP_DECLARE_TRI_LAUNCHERS(M) \
+    TP_DECLARE_TRI_LAUNCHER(M, 0) TP_DECLARE_TRI_LAUNCHER(M, 1) TP_DECLARE_TRI_LAUNCHER(M, 2) TP_DECLARE_TRI_LAUNCHER(M, 3)
+TP_DECLARE_TRI_LAUNCHERS(64)
+TP_DECLARE_TRI_LAUNCHERS(80)
 
 // Score ranks [lo, hi) of the C(n, k') lexicographic subset order of request *rq (device
 // pointer; h_rq is the host copy used for launch geometry) and leave the winner in scratch.out.

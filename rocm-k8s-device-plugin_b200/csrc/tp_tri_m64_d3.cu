@@ -1,0 +1,5 @@
+// kernel TRI, lane vectors of 64 positions, 3 walked positions above the triple (see tp_tri.cuh)
+#include "tp_kernels.cuh"
+
+#include "tp_tri.cuh"
+TP_DEFINE_TRI_LAUNCHER(64, 3)

@@ -1,0 +1,5 @@
+// kernel TRI, lane vectors of 80 positions, 1 walked position above the triple (see tp_tri.cuh)
+#include "tp_kernels.cuh"
+
+#include "tp_tri.cuh"
+TP_DEFINE_TRI_LAUNCHER(80, 1)

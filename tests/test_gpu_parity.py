@@ -252,8 +252,7 @@ def test_work_plan_with_cut_values(pols, name, monkeypatch):
     ref, pol = pols(name)
     ids = [d.Id for d in ref.devices]
     gen = topo.SplitMix64(0xC07 + len(ids))
-    monkeypatch.setenv("TP_SPLIT_CAP", "200")
-    monkeypatch.setenv("TP_SPLIT_CAP1", "150")
+    pol.set_tuning(item_cap=200, item_cap1=150)
     for size, cap in ((8, 30), (9, 26), (10, 24)):  # k' = size: D = 2, 3, 4
         for _ in range(3):
             pool = [i for i in ids if gen.chance(0.7)][:cap]

@@ -32,10 +32,9 @@ def test_c4_shards_add_up(shards):
 
 @pytest.mark.parametrize("caps", [None, ("200", "150"), ("64", "64"), ("5000", "300")])
 def test_slices_partition_the_space(caps, monkeypatch):
-    if caps:
-        monkeypatch.setenv("TP_SPLIT_CAP", caps[0])
-        monkeypatch.setenv("TP_SPLIT_CAP1", caps[1])
     pol, ids = host_policy(*topo.fixture_topology("cpx"))
+    if caps:
+        pol.set_tuning(item_cap=int(caps[0]), item_cap1=int(caps[1]))
     gen = topo.SplitMix64(0x9A17)
     for size in (4, 5, 6, 7, 8, 9, 10, 12):  # walk depths 0 .. 4
         for _ in range(3):
