@@ -248,6 +248,12 @@ bool build_plan(const tp_policy *p, Prep &out) {
     // them, and larger items spend less on the per-item set-up (unrank, lane vectors).
     if (out.batch)
         cap0 = std::min<u64>(std::max<u64>(2048, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 6)), 65536);
+    // Kernel TRI pays more per item (it builds its lane registers per walked prefix, and an item that
+    // covers only part of a prefix runs the generic pass), so its items are larger: the longest one
+    // (the heaviest run first) about 45 % of what a warp has to do in the whole search.  Measured on 8 of 64:
+    // 0.400 ms at 4 K, 0.352 at 11 K, 0.314 at 64 K, 0.449 at 128 K subsets per lane and item.
+    if (tri_gcap > 0 && !out.batch)
+        cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (72000ull * (u64)std::max(out.shards, 1))), 262144);
     if (p->tune_cap) cap0 = std::max<u64>(64, p->tune_cap); // tuning aid
     // Single values of b0 become items of their own, cut by b1 (D >= 2 only) -- only where it matters:
     // when one value alone is more than a quarter of what a lane has to do in this search (shard);

@@ -82,8 +82,8 @@ static __device__ __forceinline__ TpKey tp_warp_min_key(TpKey k) {
 
 // Block-wide min of the per-thread winners, then the cross-block step: every block stores
 // its partial, the last one to arrive (ticket) reduces all partials into scratch.out and
-// re-arms the scratch for the next launch.
-static __device__ void tp_block_finish(TpKey best, u64 counted, const TpScratch &sc) {
+// re-arms the scratch for the next launch.  Returns true in every thread of that last block.
+static __device__ bool tp_block_finish(TpKey best, u64 counted, const TpScratch &sc) {
     __shared__ TpKey s_red[32];
     __shared__ u64 s_cnt[32];
     __shared__ bool s_last;
@@ -115,7 +115,7 @@ static __device__ void tp_block_finish(TpKey best, u64 counted, const TpScratch 
         }
     }
     __syncthreads();
-    if (!s_last) return;
+    if (!s_last) return false;
     __threadfence();
     TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
     for (unsigned i = threadIdx.x; i < gridDim.x; i += blockDim.x) {
@@ -135,6 +135,7 @@ static __device__ void tp_block_finish(TpKey best, u64 counted, const TpScratch 
             *sc.ticket = 0u;
         }
     }
+    return true;
 }
 
 // Block-wide (min key, sum count); the result is valid in thread 0.  Ends with a __syncthreads,

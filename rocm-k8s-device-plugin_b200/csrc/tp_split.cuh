@@ -906,7 +906,9 @@ tp_exhaustive_split(const uint8_t *__restrict__ W, int nd, const u64 *__restrict
                 batch.results[out].scored = counted;
             }
         } else {
-            tp_block_finish(best, counted, sc); // the work counter is re-armed by the launcher's memset
+            // (the launcher's memset arms the work counter; the last block also leaves it at zero, which is
+            // what kernel TRI, sharing the word, expects to find)
+            if (tp_block_finish(best, counted, sc) && threadIdx.x == 0) *work_counter = 0u;
         }
     }
 }

@@ -43,6 +43,7 @@
 #endif
 #define TP_TRI_NREG (2 * TP_TRI_GC)
 
+
 // Row pair h of a leaf's table holds entries jy = 0..2h, padded to 16-byte chunks of four.
 __host__ __device__ constexpr int tp_tri_chunks(int h) { return (h >> 1) + 1; }
 // ... and starts at this chunk: sum of tp_tri_chunks(h') over h' < h.
@@ -117,19 +118,35 @@ __device__ __forceinline__ void tp_tri_rowpair(const unsigned (&VT)[TP_TRI_NREG]
 #ifndef TP_TRI_PREFETCH
 #define TP_TRI_PREFETCH 1
 #endif
+// Chunks are consumed row pair by row pair (H descending, c ascending); chunk (H, c) sits in buffer
+// set (S(H) + c) & 1, S(H) = chunks of the row pairs above H, so that consecutive chunks alternate.
+__host__ __device__ constexpr int tp_tri_buf(int h, int c) {
+    return (tp_tri_off(TP_TRI_GC) - tp_tri_off(h + 1) + c) & 1;
+}
+__device__ __forceinline__ unsigned tp_pack_lo(unsigned a, unsigned b) { // a.lo | b.lo << 16; volatile: computed
+    unsigned r;                                                          // where it stands, not hoisted out of the
+    asm volatile("prmt.b32 %0, %1, %2, 0x5410;" : "=r"(r) : "r"(a), "r"(b)); // pass loop into 24 more registers
+    return r;
+}
 template <int H>
 __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                                  unsigned &runA, unsigned &runB, const uint4 &curA,
-                                                  const uint4 &curB, uint4 &nxtA, uint4 &nxtB) {
+                                                  unsigned &runA, unsigned &runB, uint4 (&bA)[2], uint4 (&bB)[2]) {
     constexpr int NCH = tp_tri_chunks(H), OFF = tp_tri_off(H);
-    if constexpr (H > 0) {
-        nxtA = tp_lds128(tA + tp_tri_off(H - 1) * 16);
-        nxtB = tp_lds128(tB + tp_tri_off(H - 1) * 16);
-    }
     unsigned accA = TP_BIG2 + TP_BIG2, accB = TP_BIG2 + TP_BIG2;
 #pragma unroll
     for (int c = 0; c < NCH; c++) {
-        const uint4 a = c == 0 ? curA : tp_lds128(tA + (OFF + c) * 16), b = c == 0 ? curB : tp_lds128(tB + (OFF + c) * 16);
+        constexpr int dummy = 0;
+        (void)dummy;
+        const int cur = tp_tri_buf(H, c);
+        // the next chunk (of this row pair, or the first of the one below) starts before this one is used
+        if (c + 1 < NCH) {
+            bA[cur ^ 1] = tp_lds128v(tA + (OFF + c + 1) * 16);
+            bB[cur ^ 1] = tp_lds128v(tB + (OFF + c + 1) * 16);
+        } else if (H > 0) {
+            bA[cur ^ 1] = tp_lds128v(tA + tp_tri_off(H > 0 ? H - 1 : 0) * 16);
+            bB[cur ^ 1] = tp_lds128v(tB + tp_tri_off(H > 0 ? H - 1 : 0) * 16);
+        }
+        const uint4 a = bA[cur], b = bB[cur];
         accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
         accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
         if (4 * c + 1 <= 2 * H) {
@@ -145,7 +162,7 @@ __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NR
             accB = __viaddmin_u16x2(VT[4 * c + 3], b.w, accB);
         }
     }
-    const unsigned pk = __byte_perm(VT[2 * H], VT[2 * H + 1], 0x5410); // VT[2H] | VT[2H+1] << 16
+    const unsigned pk = tp_pack_lo(VT[2 * H], VT[2 * H + 1]); // VT[2H] | VT[2H+1] << 16
     runA = __viaddmin_u16x2(accA, pk, runA);
     runB = __viaddmin_u16x2(accB, pk, runB);
 }
@@ -153,8 +170,7 @@ __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NR
 #if TP_TRI_PREFETCH
 #define TP_TRI_CASE(H)                                                                               \
     case H:                                                                                          \
-        if constexpr ((H) & 1) tp_tri_rowpair_pf<(H)>(VT, tA, tB, runA, runB, bufA1, bufB1, bufA0, bufB0); \
-        else tp_tri_rowpair_pf<(H)>(VT, tA, tB, runA, runB, bufA0, bufB0, bufA1, bufB1);             \
+        tp_tri_rowpair_pf<(H)>(VT, tA, tB, runA, runB, bufA, bufB);                                  \
         [[fallthrough]];
 #else
 #define TP_TRI_CASE(H)                                   \
@@ -189,6 +205,31 @@ __device__ __forceinline__ void tp_tri_vt_chunk(unsigned (&VT)[TP_TRI_NREG], uns
 // What the hot loop does not need in registers lives here: the block's tables (written once per
 // request) and, per warp, the item it is on.  The slow path rebuilds its view from these, so that
 // the leaf loop carries the 64 lane registers and little else.
+// Phase timestamps of block 0 (tuning aid, compiled only with -DTP_TRI_TIMING; read by tp_tri_times_m<M>_d<D>).
+#ifdef TP_TRI_TIMING
+static __device__ unsigned long long tp_tri_times[16];
+#define TP_TRI_STAMP(i)                                                      \
+    do {                                                                     \
+        if (blockIdx.x == 0 && threadIdx.x == 0) {                           \
+            unsigned long long t__;                                          \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));          \
+            tp_tri_times[i] = t__;                                           \
+        }                                                                    \
+    } while (0)
+// slots 9 / 10: earliest entry and latest exit over ALL blocks (10 must be zeroed by the reader between runs)
+#define TP_TRI_STAMP_ALL(i, op)                                              \
+    do {                                                                     \
+        if (threadIdx.x == 0) {                                              \
+            unsigned long long t__;                                          \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t__));          \
+            op(&tp_tri_times[i], t__);                                       \
+        }                                                                    \
+    } while (0)
+#else
+#define TP_TRI_STAMP(i) ((void)0)
+#define TP_TRI_STAMP_ALL(i, op) ((void)0)
+#endif
+
 struct TpTriBlock {
     TpSplitShared sh;
     TpSmem s;
@@ -199,10 +240,13 @@ struct TpTriBlock {
     int gcap;
     int c_req, jt_hi, n_entries, b_star;
     unsigned total_items;
+    unsigned *g_bound_inv; // see tp_tri_setup
 };
 static __shared__ TpTriBlock tp_tri_blk;
 static __shared__ int tp_tri_bound;                          // best Family score seen by the block
 static __shared__ uint16_t tp_tri_pair_start[TP_TRI_GC + 1]; // first chunk of every leaf pair
+// per leaf pair g, in bytes: table of leaf 2g+1, distance to the table of leaf 2g+2, first chunk of row pair g
+static __shared__ uint4 tp_tri_pair_info[TP_TRI_GC];
 // the plan's per-pivot tables (item -> pivot lookups happen once per item)
 static __shared__ uint32_t tp_tri_item_base[TP_MAX_N], tp_tri_n_chunks[TP_MAX_N];
 static __shared__ uint8_t tp_tri_pieces[TP_MAX_N];
@@ -269,6 +313,7 @@ __device__ __noinline__ void tp_tri_slow(int b_leaf, int base, TpKey *best) {
 // Offsets inside a warp's area: [DW+1][M] T vectors, [M/8][32] lane vectors (16 bytes each), byte area.
 #define TP_TRI_VA_OFF(M, DW) ((unsigned)((DW) + 1) * (M) * 2u)
 #define TP_TRI_WB_OFF(M, DW) (TP_TRI_VA_OFF(M, DW) + (unsigned)((M) / 8) * 512u)
+
 
 struct TpTriHot { // what the walk keeps in registers: 32-bit shared addresses and a few numbers
     unsigned wb;  // the warp's area
@@ -358,9 +403,8 @@ __device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned tl, unsigned
     unsigned VT[TP_TRI_NREG];
     const int vt_chunks = min((hi + 7) >> 3, TP_TRI_NREG / 8);
     const int gcap = abs(gcap_active);
-    auto vt_at = [&](int j) -> int { // (V + T)[j] of this lane
-        const unsigned pk = tp_lds32(va + (unsigned)((j >> 3) * 512 + ((j >> 1) & 3) * 4));
-        return (int)((j & 1) ? (pk >> 16) : (pk & 0xFFFF)) + (int)tp_lds16(tl + 2u * (unsigned)j);
+    auto vt_at = [&](int j) -> int { // (V + T)[j] of this lane: two 16-bit loads
+        return (int)tp_lds16(va + (unsigned)((j >> 3) * 512 + (j & 7) * 2)) + (int)tp_lds16(tl + 2u * (unsigned)j);
     };
     const int room = *(volatile int *)&tp_tri_bound - base + 1; // a total below this is a candidate
     // (a lane without a real A never reports: its threshold is 0)
@@ -385,12 +429,14 @@ __device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned tl, unsigned
                 xA = xB = 0u;
                 goto rare;
             }
-            const unsigned tB = tbl + 16u * tp_tri_pair_start[g];
-            const unsigned tA = tB + 8u * (unsigned)(tp_tri_pair_start[g + 1] - tp_tri_pair_start[g]);
+            const uint4 pi = tp_tri_pair_info[g];
+            const unsigned tB = tbl + pi.x, tA = tB + pi.y;
             unsigned runA = TP_BIG2 + TP_BIG2, runB = TP_BIG2 + TP_BIG2;
 #if TP_TRI_PREFETCH
-            const unsigned off_g = 16u * (unsigned)((g & 1) ? ((g >> 1) + 1) * ((g >> 1) + 1) : (g >> 1) * ((g >> 1) + 1));
-            uint4 bufA0 = tp_lds128(tA + off_g), bufB0 = tp_lds128(tB + off_g), bufA1 = bufA0, bufB1 = bufB0;
+            const unsigned off_g = pi.z;
+            uint4 bufA[2], bufB[2]; // (the entry chunk goes to both sets: which one row pair g reads is a compile-time fact)
+            bufA[0] = bufA[1] = tp_lds128v(tA + off_g);
+            bufB[0] = bufB[1] = tp_lds128v(tB + off_g);
 #endif
             switch (g) {
 #if TP_TRI_GC > 24
@@ -399,7 +445,8 @@ __device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned tl, unsigned
                 TP_TRI_CASE8(16) TP_TRI_CASE8(8) TP_TRI_CASE8(0)
             default: break;
             }
-            const int vbA = vt_at(min(bA, hi - 1)), vbB = vt_at(bB); // (bA == hi can be one past the lane vector)
+            // the leaves' own terms (bA == hi is not a leaf, and can be one past the lane vector)
+            const int vbA = vt_at(min(bA, hi - 1)), vbB = vt_at(bB);
             xA = bA < hi ? runA + (unsigned)vbA * 0x10001u : 0xFFFFFFFFu;
             xB = bB >= lo ? runB + (unsigned)vbB * 0x10001u : 0xFFFFFFFFu;
             if (__vminu2(__vminu2(xA, xB), room2) != room2) goto rare;
@@ -543,6 +590,12 @@ __device__ __noinline__ bool tp_tri_item_setup(unsigned item, TpTriItem *out) {
         if (!tp_split_slice(C, cum, jt, q, (int)tp_tri_pieces[e], blk.b_star, (int)slice, sl)) return false; // empty
     }
     __syncwarp(); // the previous item's slow-path lanes are done with the warp's areas
+    if (lane == 0 && blk.g_bound_inv) { // what other blocks found so far, and what this one did
+        const int theirs = (int)(0x7FFFFFFFu - *(volatile unsigned *)blk.g_bound_inv);
+        const int ours = *(volatile int *)&tp_tri_bound;
+        if (theirs < ours) atomicMin(&tp_tri_bound, theirs);
+        else if (ours < theirs) atomicMax(blk.g_bound_inv, 0x7FFFFFFFu - (unsigned)ours);
+    }
     {
         u64 per_lane; // sets below the lane set that this item scores per lane
         if (sl.cut_again) per_lane = C(sl.b1_hi, q - 1) - C(sl.b1_lo, q - 1);
@@ -603,22 +656,62 @@ __device__ __noinline__ bool tp_tri_item_setup(unsigned item, TpTriItem *out) {
     return true;
 }
 
-// Once per request and block: stage the request, build the tables, seed the bound.
+// Exact seed, spread over (mask of whole groups, partial group) units: every Family member is one
+// unit (h == n_groups stands for "no partial group").  Thread `first` of `stride` takes units
+// first, first + stride, ...: the whole block for a batch request, the whole GRID for a single
+// request (each block then scores a 1/gridDim share and publishes its best through global memory).
+static __device__ __noinline__ int tp_tri_family_seed(const TpSmem s, int n_groups, int k, int c_req, unsigned first,
+                                                      unsigned stride) {
+    int best = 0x7FFFFFFF;
+    if (n_groups > TP_SEED_MAX_GROUPS) return best;
+    const unsigned per = (unsigned)n_groups + 1u, total = (1u << n_groups) * per;
+    for (unsigned unit = first; unit < total; unit += stride) {
+        const unsigned mask = unit / per;
+        const int h = (int)(unit - mask * per);
+        if (h < n_groups && ((mask >> h) & 1u)) continue;
+        int size = 0;
+        for (unsigned m = mask; m && size <= k; m &= m - 1) size += s.gsize[__ffs(m) - 1];
+        const int r = k - size; // devices still to take: a proper prefix of group h
+        if (r < 0 || (h == n_groups ? r != 0 : (r == 0 || s.gsize[h] <= r))) continue;
+        int pos[TP_MAX_K];
+        int cnt = 0;
+        for (unsigned m = mask; m; m &= m - 1) {
+            const int g = __ffs(m) - 1;
+            for (int t = 0; t < s.gsize[g]; t++) pos[cnt++] = s.gstart[g] + t;
+        }
+        for (int t = 0; t < r; t++) pos[cnt++] = s.gstart[h] + t; // the prefix (order does not matter here)
+        int sco = c_req;
+        for (int i = 0; i < cnt; i++) {
+            sco += s.u[pos[i]];
+            for (int j = 0; j < i; j++) sco += s.w[pos[j] * s.stride + pos[i]];
+        }
+        best = min(best, sco);
+    }
+    return best;
+}
+
+// Once per request and block: stage the request, build the tables, seed the bound.  Three
+// barriers: (1) the descriptor's small tables, (2) the weights in canonical order (gathered
+// from global memory straight into the byte table and the 16-bit reversed table), (3) the S3
+// table and the seeds.  g_bound_inv: a global word shared by the grid (single request) through
+// which blocks exchange the best Family score they know, stored as 0x7FFFFFFF - score so that a
+// zeroed word means "none"; null for a batch request, where the block owns the request.
 template <int M, int DW>
 __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__ binom_g,
-                                          const TpReq *__restrict__ rq, const TpPlan *__restrict__ plan) {
+                                          const TpReq *__restrict__ rq, const TpPlan *__restrict__ plan,
+                                          unsigned *g_bound_inv) {
     unsigned char *const smem = tp_split_smem;
     __shared__ uint8_t s_hmap[tp_tri_off(TP_TRI_GC)];
-    const int n = rq->n, k = rq->k;
+    __shared__ uint8_t s_canon[TP_MAX_N], s_req[TP_MAX_N];
+    const int n = rq->n, k = rq->k, n_req = rq->n_req;
     const int gcap = plan->tri_gcap;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x, nt = blockDim.x;
     // layout: the S3 table first (+ a zero the compiler cannot see, so that its base lives in a
     // register and rows are addressed [base + constant]), then the staged request, the plain
     // table, u, and the per-warp areas
     uint4 *tbl = (uint4 *)smem + (plan->p >> 24);
     size_t off = tp_tri_table_bytes(gcap);
     const TpSmem s = tp_smem_carve(smem + off, n, k);
-    tp_stage_request(s, W, nd, binom_g, rq, k, &tp_tri_bound);
     off += (tp_smem_bytes(n, k) + 15) & ~(size_t)15;
     const int rsp = tp_split_rsp(n);
     uint16_t *wp = (uint16_t *)(smem + off);
@@ -629,7 +722,9 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
     unsigned char *warp_base = smem + off + (size_t)warp * per_warp;
     uint16_t *tstack = (uint16_t *)warp_base; // [DW+1][M]
     uint8_t *bstack = warp_base + (size_t)(DW + 1) * M * 2 + (size_t)(M / 8) * 32 * 16;
-    if (threadIdx.x == 0) {
+    TP_TRI_STAMP(1);
+    // ---- (1) everything that is a plain copy or a formula ------------------------------------
+    if (tid == 0) {
         tp_tri_blk.sh = TpSplitShared{wp, nullptr, n, k, plan->p, plan->q, rq->dbits, rsp, plan->min_w};
         tp_tri_blk.s = s;
         tp_tri_blk.tbl = tbl;
@@ -642,43 +737,97 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         tp_tri_blk.n_entries = plan->n_entries;
         tp_tri_blk.b_star = plan->b_star;
         tp_tri_blk.total_items = plan->total_items;
+        tp_tri_blk.g_bound_inv = g_bound_inv;
+        tp_tri_bound = 0x7FFFFFFF;
     }
     if (lane == 0) *(u64 *)(bstack + TP_TRI_WB_COUNT) = 0;
-    for (int j = warp; j < n; j += TP_TRI_WARPS) { // one table row per warp pass: no divisions
-        const uint8_t *src = s.w + (n - 1 - j) * s.stride + (n - 1);
-        for (int jj = lane; jj < rsp; jj += 32) // plain table, padding 0 (it is summed)
-            wp[j * rsp + jj] = (jj < n && jj != j) ? (uint16_t)src[-jj] : (uint16_t)0;
+    for (int i = tid; i < n; i += nt) {
+        s_canon[i] = rq->canon[i];
+        s.group[i] = rq->group_of[i];
+        s.gstart[i] = rq->gstart[i];
+        s.gsize[i] = rq->gsize[i];
     }
-    for (int i = threadIdx.x; i < TP_MAX_N; i += blockDim.x) t0[i] = i < n ? s.u[n - 1 - i] : (uint16_t)0;
-    for (int g = threadIdx.x; g <= gcap; g += blockDim.x) tp_tri_pair_start[g] = (uint16_t)tp_tri_pair_base(g);
-    for (int h = threadIdx.x; h < gcap; h += blockDim.x)
+    for (int i = tid; i < n_req; i += nt) s_req[i] = rq->req[i];
+    for (int a = warp; a <= n; a += TP_TRI_WARPS)
+        for (int j = lane; j <= k; j += 32) s.binom[a * (k + 1) + j] = binom_g[a * TP_BINOM_COLS + j];
+    for (int i = tid; i < plan->n_entries; i += nt) {
+        tp_tri_item_base[i] = plan->item_base[i];
+        tp_tri_n_chunks[i] = plan->n_chunks[i];
+        tp_tri_pieces[i] = plan->n_pieces[i];
+    }
+    for (int i = tid; i < TP_MAX_N + 2; i += nt) tp_tri_cum[i] = plan->cum[i];
+    for (int g = tid; g <= gcap; g += nt) tp_tri_pair_start[g] = (uint16_t)tp_tri_pair_base(g);
+    for (int g = tid; g < gcap; g += nt)
+        tp_tri_pair_info[g] = make_uint4(16u * tp_tri_pair_base(g), 16u * tp_tri_off(g + 1), 16u * tp_tri_off(g), 0u);
+    for (int h = tid; h < gcap; h += nt)
         for (int c = tp_tri_off(h); c < tp_tri_off(h + 1); c++) s_hmap[c] = (uint8_t)h;
-    if (threadIdx.x == 0 && rq->n_groups > TP_SEED_MAX_GROUPS) { // second seed where the exact one does not run:
-        // whole groups from the largest down (also a Family member)
+    __syncthreads();
+    TP_TRI_STAMP(2);
+    // ---- (2) weights: canonical byte table (seeds) and 16-bit reversed table (everything else) ----
+    for (int r = warp; r < n; r += TP_TRI_WARPS) { // one row per warp pass: no divisions
+        const uint8_t *wrow = W + (int)s_canon[r] * nd;
+        uint16_t *prow = wp + (n - 1 - r) * rsp;
+        for (int c = lane; c < rsp; c += 32) { // reversed column n - 1 - c holds canonical column c
+            const unsigned v = (c < n && c != r) ? wrow[s_canon[c]] : 0u;
+            if (c < n) {
+                s.w[r * s.stride + c] = (uint8_t)v;
+                prow[n - 1 - c] = (uint16_t)v;
+            } else {
+                prow[c] = 0; // padding (it is summed)
+            }
+        }
+    }
+    for (int i = tid; i < TP_MAX_N; i += nt) {
+        unsigned u = 0;
+        if (i < n) {
+            const uint8_t *wrow = W + (int)s_canon[i] * nd;
+            for (int r = 0; r < n_req; r++) u += wrow[s_req[r]];
+            s.u[i] = (uint16_t)u;
+            t0[n - 1 - i] = (uint16_t)u;
+        } else {
+            t0[i] = 0;
+        }
+    }
+    __syncthreads();
+    TP_TRI_STAMP(3);
+    // ---- (3) seeds (a few threads; Family members all) and the S3 table (everybody) ----------
+    if (tid == nt - 1 || tid == nt - 2) {
+        // canonical positions {0..k-1}, and whole groups from the largest down
         int left = k, sco = rq->c_req, cnt = 0;
         int pos[TP_MAX_K];
-        for (int g = rq->n_groups - 1; g >= 0 && left > 0; g--) {
-            const int take = min((int)s.gsize[g], left);
-            for (int t = 0; t < take; t++) pos[cnt++] = s.gstart[g] + t;
-            left -= take;
+        if (tid == nt - 1) {
+            for (int i = 0; i < k; i++) pos[cnt++] = i;
+            left = 0;
+        } else {
+            for (int g = rq->n_groups - 1; g >= 0 && left > 0; g--) {
+                const int take = min((int)s.gsize[g], left);
+                for (int t = 0; t < take; t++) pos[cnt++] = s.gstart[g] + t;
+                left -= take;
+            }
         }
         for (int i = 0; i < cnt; i++) {
             sco += s.u[pos[i]];
             for (int j = 0; j < i; j++) sco += s.w[pos[j] * s.stride + pos[i]];
         }
-        if (left == 0 && sco < tp_tri_bound) atomicMin(&tp_tri_bound, sco);
+        if (left == 0) atomicMin(&tp_tri_bound, sco);
     }
-    tp_split_family_seed(s, rq->n_groups, k, rq->c_req, &tp_tri_bound);
-    __syncthreads();
+    {
+        // A share per block only where the whole seed would cost a block microseconds AND the search is
+        // long enough for the other blocks' shares to arrive early in it; a small search is mostly over
+        // by then, and with a loose bound most of its leaves would go through the slow path.
+        const bool spread = g_bound_inv && ((1u << min(rq->n_groups, 20)) * (unsigned)(rq->n_groups + 1) > 4096u) &&
+                            rq->total > (1ull << 28);
+        const unsigned first = spread ? blockIdx.x * (unsigned)nt + tid : (unsigned)tid;
+        const unsigned stride = spread ? gridDim.x * (unsigned)nt : (unsigned)nt;
+        const int sco = tp_tri_family_seed(s, rq->n_groups, k, rq->c_req, first, stride);
+        if (sco != 0x7FFFFFFF) atomicMin(&tp_tri_bound, sco);
+    }
+    TP_TRI_STAMP(4);
     tp_tri_build_table(tbl, tp_tri_pair_start, s_hmap, gcap, wp, rsp);
+    TP_TRI_STAMP(5);
     for (int i = lane; i < M; i += 32) tstack[i] = t0[i];
-    for (int i = threadIdx.x; i < plan->n_entries; i += blockDim.x) {
-        tp_tri_item_base[i] = plan->item_base[i];
-        tp_tri_n_chunks[i] = plan->n_chunks[i];
-        tp_tri_pieces[i] = plan->n_pieces[i];
-    }
-    for (int i = threadIdx.x; i < TP_MAX_N + 2; i += blockDim.x) tp_tri_cum[i] = plan->cum[i];
     __syncthreads();
+    if (tid == 0 && g_bound_inv) atomicMax(g_bound_inv, 0x7FFFFFFFu - (unsigned)tp_tri_bound);
 }
 
 // Single request (batch.count == 0): the whole grid shares the request and its item counter, the
@@ -710,7 +859,12 @@ tp_exhaustive_tri(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
         } else if (iter > 0) {
             break;
         }
-        tp_tri_setup<M, DW>(W, nd, binom_g, reqs + slot, plans + plan);
+        TP_TRI_STAMP(0);
+        TP_TRI_STAMP_ALL(9, atomicMin);
+        TP_TRI_STAMP_ALL(11, atomicMax);
+        tp_tri_setup<M, DW>(W, nd, binom_g, reqs + slot, plans + plan, batch.count > 0 ? nullptr : work_counter + 1);
+        TP_TRI_STAMP(6);
+        TP_TRI_STAMP_ALL(12, atomicMax);
         TpKey best = {TP_KEY_INF_HI, TP_KEY_INF_HI}; // (its address goes to the callees: it lives in the frame)
         const int lane = threadIdx.x & 31;
         // the warp's areas, by 32-bit shared address
@@ -736,6 +890,8 @@ tp_exhaustive_tri(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
             __syncwarp();
         }
         __syncwarp();
+        TP_TRI_STAMP(7);
+        TP_TRI_STAMP_ALL(13, atomicMax);
         u64 counted = 0;
         if (lane == 0) {
             unsigned clo, chi;
@@ -749,7 +905,14 @@ tp_exhaustive_tri(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
                 batch.results[out].scored = counted;
             }
         } else {
-            tp_block_finish(best, counted, sc); // the work counter is re-armed by the launcher's memset
+            // the last block to finish re-arms the two words of work_counter for the next launch (no memset in
+            // the launcher: one stream operation less per search)
+            if (tp_block_finish(best, counted, sc) && threadIdx.x == 0) {
+                work_counter[0] = 0u;
+                work_counter[1] = 0u;
+            }
+            TP_TRI_STAMP(8);
+            TP_TRI_STAMP_ALL(10, atomicMax);
         }
     }
 }
@@ -772,8 +935,10 @@ static cudaError_t launch_tri_md(const uint8_t *W, int nd, const u64 *binom, con
     cudaError_t e = cudaFuncSetAttribute(tp_exhaustive_tri<M, DW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)smem);
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(batch.count > 0 ? batch.grab : d_counter, 0, sizeof(unsigned), st);
-    if (e != cudaSuccess) return e;
+    if (batch.count > 0) { // (a single request's counter words are re-armed by the kernel itself)
+        e = cudaMemsetAsync(batch.grab, 0, sizeof(unsigned), st);
+        if (e != cudaSuccess) return e;
+    }
     int blocks = sm_count;
     if (batch.count > 0 && batch.count < blocks) blocks = batch.count;
     tp_exhaustive_tri<M, DW><<<blocks, TP_TRI_THREADS, smem, st>>>(W, nd, binom, d_rq, d_plan, shard_idx, shard_cnt,
@@ -786,6 +951,18 @@ static cudaError_t launch_tri_md(const uint8_t *W, int nd, const u64 *binom, con
     return cudaGetLastError();
 }
 
+#ifdef TP_TRI_TIMING
+#define TP_TRI_TIMES_READER(M, D)                                                                        \
+    extern "C" int tp_tri_times_m##M##_d##D(unsigned long long *out) {                                   \
+        int rc = (int)cudaMemcpyFromSymbol(out, tp_tri_times, sizeof(tp_tri_times));                     \
+        unsigned long long reset[16];                                                                    \
+        for (int i = 0; i < 16; i++) reset[i] = i == 9 ? ~0ull : 0ull;                                   \
+        cudaMemcpyToSymbol(tp_tri_times, reset, sizeof(reset));                                          \
+        return rc;                                                                                       \
+    }
+#else
+#define TP_TRI_TIMES_READER(M, D)
+#endif
 // One translation unit per (M, DW) defines these for its instantiation.
 #define TP_DEFINE_TRI_LAUNCHER(M, D)                                                                             \
     cudaError_t tp_launch_tri_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,            \
@@ -795,4 +972,5 @@ static cudaError_t launch_tri_md(const uint8_t *W, int nd, const u64 *binom, con
         return launch_tri_md<M, D>(W, nd, binom, d_rq, h, d_plan, gcap, si, sn, sc, d_counter, sms, st, info,   \
                                    batch);                                                                       \
     }                                                                                                            \
-    size_t tp_tri_smem_m##M##_d##D(int n, int k, int gcap) { return tp_tri_smem_bytes_md<M, D>(n, k, gcap); }
+    size_t tp_tri_smem_m##M##_d##D(int n, int k, int gcap) { return tp_tri_smem_bytes_md<M, D>(n, k, gcap); }   \
+    TP_TRI_TIMES_READER(M, D)
