@@ -202,8 +202,14 @@ void tp_prepared_free(tp_policy *p, tp_prepared *q);
  *     that the call returns TP_ERR_STATIC_SCRATCH and does no GPU work;
  *   - the array is shared: calls whose GPU work overlaps on one device corrupt each other,
  *     so run them one after another (the call itself blocks until its result is on the host);
- *   - the first call on each GPU looks up the array's address and uploads a small constant
- *     table, synchronising `cuda_stream`: make that first call before any stream capture.
+ *   - the first call on each GPU looks up the array's address, loads the code of the sixteen
+ *     kernel variants it may launch later (one per size - n_required; loading code takes
+ *     device memory, so it is done up front, not on a later request) and uploads a small constant
+ *     table, synchronising `cuda_stream`: make that first call early, before any stream capture
+ *     and while memory is still to be had;
+ *   - it always runs the plain rank-range kernel (LEX), not the fast ones behind tp_allocate: an
+ *     8-of-80 request that tp_allocate answers in ~1.6 ms takes ~220 ms here.  It is a fallback for
+ *     the moment allocation is impossible, not a second fast path.
  * Runs on the CURRENT device, which must own d_weight, d_out and cuda_stream (a cudaStream_t,
  * NULL for the default stream).  Same return values as tp_allocate otherwise.
  */

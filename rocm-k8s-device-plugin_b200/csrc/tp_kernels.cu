@@ -659,13 +659,32 @@ static __device__ __align__(256) unsigned char tp_static_scratch[TP_STATIC_SCRAT
 static unsigned char *g_static_ptr[TP_STATIC_MAX_GPUS];
 static std::mutex g_static_mu;
 
-// First call on a device: resolve the array's device address and park the binomial table in
-// it.  Do this first call outside any stream capture (it synchronises the stream).
+template <int K>
+static cudaError_t tp_static_warm_one() {
+    cudaFuncAttributes a;
+    return cudaFuncGetAttributes(&a, tp_exhaustive_lex<K>);
+}
+static cudaError_t tp_static_warm_all() {
+    cudaError_t e = cudaSuccess;
+#define TP_WARM(KK) if (e == cudaSuccess) e = tp_static_warm_one<KK>();
+    TP_WARM(1) TP_WARM(2) TP_WARM(3) TP_WARM(4) TP_WARM(5) TP_WARM(6) TP_WARM(7) TP_WARM(8)
+    TP_WARM(9) TP_WARM(10) TP_WARM(11) TP_WARM(12) TP_WARM(13) TP_WARM(14) TP_WARM(15) TP_WARM(16)
+#undef TP_WARM
+    return e;
+}
+
+// First call on a device: resolve the array's device address, load the code of every kernel the
+// entry point can launch, and park the binomial table in the array.  Do this first call outside any stream capture (it synchronises the stream).
 static cudaError_t tp_static_setup(int dev, const u64 *h_binom, cudaStream_t st, unsigned char **out) {
     std::lock_guard<std::mutex> lk(g_static_mu);
     if (!g_static_ptr[dev]) {
         unsigned char *ptr = nullptr;
         cudaError_t e = cudaGetSymbolAddress((void **)&ptr, tp_static_scratch);
+        if (e != cudaSuccess) return e;
+        // Touch every instantiation the entry point can launch: with lazy module loading the first launch of
+        // a kernel loads its code, which takes device memory and can stall -- it must not happen on a later
+        // request with a k' this GPU has not seen yet, when the memory may be gone.
+        e = tp_static_warm_all();
         if (e != cudaSuccess) return e;
         e = cudaMemcpyAsync(ptr + TP_STATIC_OFF_BINOM, h_binom, (size_t)(TP_MAX_N + 1) * TP_BINOM_COLS * 8,
                             cudaMemcpyHostToDevice, st);

@@ -64,3 +64,16 @@ def test_host_sysfs_reader_matches_golden(name, tree):
         assert "GPU policy init failed" in str(e)
     assert pol.pairs() == sorted(pairs)
     assert pol.weight_rows() == topo.golden("topologies.json")[name]["weight_rows"]
+
+
+@pytest.mark.parametrize("name", ["mi308", "mi210", "cpx"])
+def test_host_sysfs_reader_on_materialised_tree(name, tmp_path):
+    """Same check from the distilled trees of tests/golden/sysfs_trees.json.gz (what the GPU box parses)."""
+    devs, pairs = topo.fixture_topology(name)
+    pol = tp.BestEffortPolicy()
+    try:
+        pol.Init([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs],
+                 topo.materialize_sysfs_tree(name, str(tmp_path)))
+    except tp.AllocatorError as e:  # no GPU here: tp_create fails after the parse
+        assert "GPU policy init failed" in str(e)
+    assert pol.pairs() == sorted(pairs)

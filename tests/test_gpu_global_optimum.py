@@ -50,7 +50,7 @@ def test_random_requests(name):
         if name != "missing":
             assert adv == pol.last["score"]
         beaten += adv < pol.last["score"]
-    assert tp.KERNEL_SPLIT in kernels or len(ids) <= 8
+    assert kernels & {tp.KERNEL_SPLIT, tp.KERNEL_TRI} or len(ids) <= 8
     if name == "missing":
         assert beaten > 5
     pol.close()
@@ -81,7 +81,7 @@ def test_full_size_searches():
         got = pol.GlobalOptimum(ids, [], 8)
         assert got == want and pol.last["score"] == ref.last["score"]
         assert pol.last["subsets_scored"] == want_total == ref.last["total"]
-        assert pol.last["kernel"] == tp.KERNEL_SPLIT and pol.last["key"][1] != 0
+        assert pol.last["kernel"] == tp.KERNEL_TRI and pol.last["key"][1] != 0
         adv = pol.last["score"]
         pol.Allocate(ids, [], 8)
         assert adv == pol.last["score"]

@@ -133,16 +133,74 @@ def test_shards_cover_the_space(pols):
         assert pol.Decode(av, rq, k, min(keys)) == want
 
 
+def test_full_size_headline_searches(pols):
+    """BASELINE configs at full size against the reference policy's ids (ordered): C4 = 8 of 80
+    (28 987 537 150 subsets), 8 of 64 (the 4.4e9 figure of C3) and 7 of 80, every subset counted."""
+    for name, n_take, size, total in (("c4", 80, 8, 28987537150), ("cpx64", 64, 8, 4426165368), ("c4", 80, 7, 3176716400)):
+        ref, pol = pols(name)
+        ids = [d.Id for d in ref.devices][:n_take]
+        want = ref.Allocate(ids, [], size)
+        got = pol.Allocate(ids, [], size)
+        assert got == want, (name, got, want)
+        assert pol.last["score"] == ref.last["score"] and pol.last["subsets_scored"] == total
+        assert pol.last["kernel"] == tp.KERNEL_TRI
+    # ... and with required devices and a ragged pool on the 80-device topology
+    ref, pol = pols("c4")
+    ids = [d.Id for d in ref.devices]
+    pool = [i for n, i in enumerate(ids) if n % 11 != 3]
+    for rq, size in (([pool[40]], 8), ([pool[3], pool[70]], 9)):
+        assert pol.Allocate(pool, rq, size) == ref.Allocate(pool, rq, size)
+        assert pol.last["score"] == ref.last["score"] and pol.last["subsets_scored"] == pol.last["subsets_total"]
+
+
+@pytest.mark.parametrize("name", ["cpx", "c4", "missing", "hives", "mi308"])
+def test_tri_kernel_walk_depths_and_widths(pols, name):
+    """Kernel TRI: k' = 6..12 (0..3 walked positions above the triple), both lane-vector widths, pools
+    wide enough for leaves above the table cap (the pruned re-walk), required devices, and shards;
+    the forced SPLIT kernel must return the same key."""
+    ref, pol = pols(name)
+    devs = ref.devices
+    pairs = topo.fixture_topology(name)[1] if name in FIXTURES else SYNTH[name]()[1]
+    spl = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_SPLIT)
+    spl.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+    ids = [d.Id for d in devs]
+    gen = topo.SplitMix64(0x7A1 ^ len(ids))
+    seen = 0
+    for kp, cap in ((6, 80), (7, 60), (8, 44), (9, 30), (10, 26), (11, 24), (12, 22)):
+        for trial in range(3):
+            n = min(len(ids), cap - gen.below(6))
+            pool = sorted(ids, key=lambda _: gen.next())[:n] if trial else ids[:n]
+            nreq = gen.below(3) if trial == 2 else 0
+            rq, size = pool[:nreq], kp + nreq
+            if len(pool) <= size + 1:
+                continue
+            want = ref.Allocate(pool, rq, size)
+            got = pol.Allocate(pool, rq, size)
+            assert got == want, (name, kp, len(pool), rq)
+            assert pol.last["score"] == ref.last["score"] and pol.last["subsets_scored"] == pol.last["subsets_total"]
+            if pol.last["subsets_total"] > 32768:
+                assert pol.last["kernel"] == tp.KERNEL_TRI
+                seen += 1
+            assert spl.Allocate(pool, rq, size) == want and spl.last["key"] == pol.last["key"]
+            keys = [pol.SearchShard(pool, rq, size, s, 3) for s in range(3)]
+            assert pol.Decode(pool, rq, size, min(keys)) == want
+    assert seen >= 6
+    spl.close()
+
+
 @pytest.mark.parametrize("name,sizes", [("mi308", range(4, 13)), ("cpx", (4, 5, 6, 7)), ("c4", (4, 5, 6)),
                                         ("missing", range(4, 11)), ("hives", range(4, 12))])
 def test_split_kernel_all_depths(pols, name, sizes):
-    """Kernel SPLIT (k' >= 4): every walk depth D = 0..4 and both lane-vector widths (M = 64, 96),
-    LEX and SPLIT must agree with the oracle and with each other."""
+    """Kernels SPLIT (k' >= 4, every walk depth D = 0..4) and TRI (k' >= 6, every walk depth 0..3): LEX,
+    SPLIT (forced) and the default choice (TRI from k' = 6 on) must agree with the oracle and with
+    each other, key for key."""
     ref, pol = pols(name)
     devs = ref.devices
+    pairs = topo.fixture_topology(name)[1] if name in FIXTURES else SYNTH[name]()[1]
     lex = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_LEX)
-    lex.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs],
-                        topo.fixture_topology(name)[1] if name in FIXTURES else SYNTH[name]()[1])
+    lex.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+    spl = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_SPLIT)
+    spl.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
     ids = [d.Id for d in devs]
     gen = topo.SplitMix64(0x5B117 + len(ids))
     seen = set()
@@ -162,8 +220,15 @@ def test_split_kernel_all_depths(pols, name, sizes):
             seen.add(pol.last["kernel"])
             assert lex.Allocate(pool, req, size) == want and lex.last["kernel"] == tp.KERNEL_LEX
             assert lex.last["key"] == pol.last["key"]
+            assert spl.Allocate(pool, req, size) == want and spl.last["key"] == pol.last["key"]
+            assert spl.last["kernel"] in (tp.KERNEL_SPLIT, tp.KERNEL_LEX)
+            seen.add(spl.last["kernel"])
+            if size - nreq >= 6 and pol.last["subsets_total"] > 32768:
+                assert pol.last["kernel"] == tp.KERNEL_TRI, (name, size, len(pool))
     assert tp.KERNEL_SPLIT in seen
+    assert tp.KERNEL_TRI in seen or max(sizes) < 6
     lex.close()
+    spl.close()
 
 
 @pytest.mark.parametrize("name", ["mi308", "cpx", "c4", "missing", "hives"])
@@ -239,17 +304,30 @@ def test_widest_topology_and_two_word_keys():
         # shards of the same request must min-reduce (two words) to the same winner
         keys = [pol.SearchShard(av, rq, k, s, 3) for s in range(3)]
         assert pol.Decode(av, rq, k, min(keys)) == want
-    assert tp.KERNEL_SPLIT in kernels and wide_keys > 0
+    assert tp.KERNEL_SPLIT in kernels and tp.KERNEL_TRI in kernels and wide_keys > 0
+    # the same deep walks through SPLIT's wide instantiations (the default picks TRI up to 80 + p devices)
+    spl = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_SPLIT)
+    spl.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+    for av, rq, k in cases[-4:] + wide_cases:
+        want = pol.Allocate(av, rq, k)
+        assert spl.Allocate(av, rq, k) == want and spl.last["kernel"] == tp.KERNEL_SPLIT
+        assert spl.last["key"] == pol.last["key"]
+    spl.close()
     pol.close()
 
 
+@pytest.mark.parametrize("kernel", [tp.KERNEL_SPLIT, tp.KERNEL_TRI])
 @pytest.mark.parametrize("name", ["cpx", "missing", "hives"])
-def test_work_plan_with_cut_values(pols, name, monkeypatch):
+def test_work_plan_with_cut_values(name, kernel):
     """The work plan's second level: single values of the first walked position cut by the second one
     (normally only for the heaviest values of large or sharded searches) is forced for every value by
     the tuning knobs, at walk depths 2, 3 and 4; answers, scored counts and the min over shards must
     not change."""
-    ref, pol = pols(name)
+    devs, pairs = topo.fixture_topology(name) if name in FIXTURES else SYNTH[name]()
+    ref = RefPolicy()
+    ref.InitPairs(devs, pairs)
+    pol = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_SPLIT if kernel == tp.KERNEL_SPLIT else tp.KERNEL_AUTO)
+    pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
     ids = [d.Id for d in ref.devices]
     gen = topo.SplitMix64(0xC07 + len(ids))
     pol.set_tuning(item_cap=200, item_cap1=150)
@@ -261,7 +339,10 @@ def test_work_plan_with_cut_values(pols, name, monkeypatch):
             want = ref.Allocate(pool, [], size)
             got = pol.Allocate(pool, [], size)
             assert got == want, (name, size, pool)
-            assert pol.last["kernel"] == tp.KERNEL_SPLIT and pol.last["score"] == ref.last["score"]
+            assert pol.last["score"] == ref.last["score"]
+            assert pol.last["kernel"] == (kernel if pol.last["subsets_total"] > 32768 or kernel == tp.KERNEL_SPLIT
+                                          else tp.KERNEL_LEX)
             assert pol.last["subsets_scored"] == pol.last["subsets_total"]
             keys = [pol.SearchShard(pool, [], size, s, 5) for s in range(5)]
             assert pol.Decode(pool, [], size, min(keys)) == want
+    pol.close()

@@ -18,6 +18,7 @@ import pytest
 
 import topo
 from __graft_entry__ import package
+from oracle.binding import RefPolicy
 
 pytestmark = pytest.mark.gpu
 tp = package()
@@ -71,6 +72,11 @@ def test_static_scratch_entry_matches_regular_entry_twice_in_a_row():
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream().cuda_stream
 
+    # the checker: the CPU restatement of the reference policy, on the same devices
+    ref = RefPolicy()
+    ref.InitPairs(devs, pairs)
+    ids = [d.Id for d in devs]
+
     gen = topo.SplitMix64(0x57A71C)
     requests = [(list(range(n)), [], 5),                       # 7 028 847 subsets, many blocks
                 (list(range(0, n, 2)), [4, 10], 6),            # required devices, k' = 4
@@ -78,7 +84,11 @@ def test_static_scratch_entry_matches_regular_entry_twice_in_a_row():
     for _ in range(3):
         av, rq, k = topo.random_request(gen, list(range(n)), kmax=6)
         requests.append((av, rq, k))
+    for k in (7, 3, 9):  # sizes whose kernel variant has not run yet: their code was loaded by the first call
+        av, rq, _ = topo.random_request(gen, list(range(30)), kmax=2)
+        requests.append((list(range(k + 9)), [], k))
     searched = 0
+    free_after_first = None
     for av, rq, k in requests:
         want = i32([0] * k)
         want_info = tp.TpResult()
@@ -86,11 +96,21 @@ def test_static_scratch_entry_matches_regular_entry_twice_in_a_row():
         for attempt in range(2):  # two calls in a row on the same shared array
             got = i32([-1] * k)
             info = tp.TpResult()
+            free_before = torch.cuda.mem_get_info(0)[0]
             rc = L.tp_allocate_static(C.byref(t), C.c_void_p(d_weight.data_ptr()), i32(av), len(av), i32(rq),
                                       len(rq), k, C.c_void_p(stream), C.c_void_p(d_out.data_ptr()), got,
                                       C.byref(info))
             assert rc == rc_want == k, (rc, rc_want, tp.strerror(min(rc, 0)))
             assert list(got[:k]) == list(want[:k]), (av, rq, k, attempt)      # bit-exact: integer indices
+            # ... and it is what the reference policy answers (ids in the reference's output order)
+            assert [ids[i] for i in got[:k]] == ref.Allocate([ids[i] for i in av], [ids[i] for i in rq], k)
+            assert info.score == ref.last["score"] or not ref.last["searched"]
+            # nothing is allocated after the first call on the device (which loads the kernels' code): free
+            # device memory is the same before and after every later call, whatever size it asks for
+            if free_after_first is not None and info.searched:
+                assert torch.cuda.mem_get_info(0)[0] == free_before, (k, attempt)
+            if info.searched:
+                free_after_first = True
             assert info.score == want_info.score and info.searched == want_info.searched
             if info.searched:
                 searched += 1

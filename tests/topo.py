@@ -147,3 +147,24 @@ def wide_topology():
             ty = 11 if int(a.DevId) // 2 == int(b.DevId) // 2 else 2
             pairs.append((a.NodeId, b.NodeId, pair_weight(a, b, ty)))
     return devs, pairs
+
+
+def materialize_sysfs_tree(name, root):
+    """Write fixture `name` of tests/golden/sysfs_trees.json.gz (see make_sysfs_trees.py) under `root` as the
+    KFD topology layout the policy parses (device.go:107-252); returns the nodes directory."""
+    import gzip
+    with gzip.open(os.path.join(GOLDEN, "sysfs_trees.json.gz"), "rt") as f:
+        nodes = json.load(f)[name]
+    top = os.path.join(root, name, "nodes")
+    for node, entry in nodes.items():
+        d = os.path.join(top, node)
+        os.makedirs(d, exist_ok=True)
+        with open(os.path.join(d, "properties"), "w") as f:
+            f.write("cpu_cores_count 0\n" + (f"drm_render_minor {entry['minor']}\n" if entry.get("minor") is not None else ""))
+        for sub in ("io_links", "p2p_links"):
+            for ln, (a, b, ty) in (entry.get(sub) or {}).items():
+                ld = os.path.join(d, sub, ln)
+                os.makedirs(ld, exist_ok=True)
+                with open(os.path.join(ld, "properties"), "w") as f:
+                    f.write("".join(f"{k} {v}\n" for k, v in (("type", ty), ("node_from", a), ("node_to", b)) if v is not None))
+    return top
