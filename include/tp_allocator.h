@@ -48,8 +48,7 @@ typedef enum tp_status {
     TP_ERR_BAD_ARGUMENT = -21,
     TP_ERR_TOO_LARGE = -22,   /* search space beyond what any kernel here enumerates */
     TP_ERR_STATIC_SCRATCH = -23, /* tp_allocate_static: request needs more than the fixed scratch holds */
-    TP_ERR_CUDA = -30,
-    TP_ERR_NCCL = -31
+    TP_ERR_CUDA = -30 /* any CUDA failure, on any of the policy's GPUs; text: tp_last_cuda_error */
 } tp_status;
 
 /*
@@ -73,12 +72,25 @@ typedef struct tp_topology {
 } tp_topology;
 
 #define TP_DEVICE_NONE (-2) /* tp_options.cuda_device: host-only handle (validation, tp_decode); searches fail */
+#define TP_MAX_GPUS 16
+/*
+ * The reference policy lives in ONE process (constructed at internal/pkg/manager/manager.go:101, called at
+ * internal/pkg/amdgpu/amdgpu.go:300-319), so more than one GPU has to be usable from one tp_policy, one call:
+ * with n_extra_devices > 0 the policy also sets itself up on extra_devices[], and a tp_allocate whose search
+ * holds at least multi_gpu_min_subsets subsets is cut into 1 + n_extra_devices shards (the same disjoint
+ * slices tp_search_shard hands out), one per GPU, launched in parallel by per-GPU worker threads; every GPU
+ * returns its packed winner to the host, which takes the minimum.  No collective library is involved: the
+ * exchange is 16 bytes per GPU.  Smaller searches, batches and the other entry points stay on cuda_device.
+ */
 typedef struct tp_options {
     int32_t cuda_device;        /* ordinal; -1 = the current device; TP_DEVICE_NONE = no device */
     int32_t kernel;             /* 0 = auto; else force a kernel variant (tests / profiling) */
     uint64_t exhaustive_limit;  /* 0 = default; above this many subsets only Family members are enumerated */
     int32_t max_inflight;       /* 0 = default (8): concurrent tp_allocate calls before callers queue */
-    int32_t reserved;
+    int32_t n_extra_devices;    /* 0 = single GPU */
+    int32_t extra_devices[TP_MAX_GPUS]; /* ordinals of the other GPUs (an ordinal may repeat: its shards then queue
+                                         * on that GPU, which is how a one-GPU box tests this path) */
+    uint64_t multi_gpu_min_subsets;     /* 0 = default (2^31) */
 } tp_options;
 
 /* Packed winner: (score, groups touched, group sequence) -- smaller is better; the
@@ -96,8 +108,8 @@ typedef struct tp_result {
     int32_t kernel;          /* kernel variant that ran */
     uint64_t subsets_scored; /* counted on the device */
     uint64_t subsets_total;  /* C(free, size-len(required)) */
-    float kernel_ms;         /* CUDA-event time of the search kernel(s) on the call's stream */
-    int32_t gpu_launches;
+    float kernel_ms;         /* CUDA-event time of the search kernel(s) on the call's stream (multi-GPU: the slowest GPU) */
+    int32_t gpu_launches;    /* kernels launched for the request, over all GPUs */
     tp_key key;
 } tp_result;
 

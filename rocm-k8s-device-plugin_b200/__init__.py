@@ -27,7 +27,7 @@ STATUS = {
     "TP_OK": 0, "TP_ERR_INVALID_SIZE": -1, "TP_ERR_INVALID_AVAILABLE": -2, "TP_ERR_INVALID_REQUIRED": -3,
     "TP_ERR_INVALID_REQ_AVAILABLE": -4, "TP_ERR_INVALID_INIT": -5, "TP_ERR_NO_CANDIDATE": -6,
     "TP_ERR_INIT_FAILED": -7, "TP_ERR_BAD_INDEX": -20, "TP_ERR_BAD_ARGUMENT": -21, "TP_ERR_TOO_LARGE": -22,
-    "TP_ERR_STATIC_SCRATCH": -23, "TP_ERR_CUDA": -30, "TP_ERR_NCCL": -31,
+    "TP_ERR_STATIC_SCRATCH": -23, "TP_ERR_CUDA": -30,
 }
 KERNEL_AUTO, KERNEL_LEX, KERNEL_SPLIT, KERNEL_FAMILY, KERNEL_TRI = 0, 1, 2, 3, 4
 
@@ -56,7 +56,8 @@ class TpResult(C.Structure):
 
 class TpOptions(C.Structure):
     _fields_ = [("cuda_device", C.c_int32), ("kernel", C.c_int32), ("exhaustive_limit", C.c_uint64),
-                ("max_inflight", C.c_int32), ("reserved", C.c_int32)]
+                ("max_inflight", C.c_int32), ("n_extra_devices", C.c_int32), ("extra_devices", C.c_int32 * 16),
+                ("multi_gpu_min_subsets", C.c_uint64)]
 
 
 class TpTopology(C.Structure):
@@ -190,8 +191,11 @@ class BestEffortPolicy:
     """allocator.BestEffortPolicy (besteffort_policy.go:45-151) backed by the GPU search."""
 
     def __init__(self, cuda_device: int = -1, kernel: int = KERNEL_AUTO, exhaustive_limit: int = 0,
-                 max_inflight: int = 0):
-        self._opts = TpOptions(cuda_device, kernel, exhaustive_limit, max_inflight, 0)
+                 max_inflight: int = 0, extra_devices=(), multi_gpu_min_subsets: int = 0):
+        """extra_devices: ordinals of further GPUs of this process; searches of at least
+        multi_gpu_min_subsets subsets (default 2^31) are then cut over all of them inside Allocate."""
+        self._opts = TpOptions(cuda_device, kernel, exhaustive_limit, max_inflight, len(extra_devices),
+                               (C.c_int32 * 16)(*extra_devices), multi_gpu_min_subsets)
         self._p = lib().tph_new(C.byref(self._opts))
         self.last = None
 

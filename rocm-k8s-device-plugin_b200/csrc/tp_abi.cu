@@ -9,6 +9,8 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <deque>
+#include <functional>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -69,8 +71,52 @@ inline int batch_shares(u64 total) { return total <= (1ull << 24) ? 1 : (int)std
 
 } // namespace
 
+namespace {
+// One thread per extra GPU: launches and collects that GPU's shard while the caller does the same on its own.
+struct GpuWorker {
+    std::mutex mu;
+    std::condition_variable cv;
+    std::deque<std::function<void()>> jobs;
+    bool stop = false;
+    std::thread th;
+    GpuWorker() : th([this] { loop(); }) {}
+    ~GpuWorker() {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            stop = true;
+        }
+        cv.notify_one();
+        th.join();
+    }
+    void submit(std::function<void()> f) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            jobs.push_back(std::move(f));
+        }
+        cv.notify_one();
+    }
+    void loop() {
+        for (;;) {
+            std::function<void()> f;
+            {
+                std::unique_lock<std::mutex> lk(mu);
+                cv.wait(lk, [&] { return stop || !jobs.empty(); });
+                if (jobs.empty()) return;
+                f = std::move(jobs.front());
+                jobs.pop_front();
+            }
+            f();
+        }
+    }
+};
+} // namespace
+
 struct tp_policy {
     int n = 0, n_groups = 0;
+    // multi-GPU: a complete policy per extra GPU (same topology) and the thread that drives it
+    std::vector<tp_policy *> peers;
+    std::vector<GpuWorker *> workers;
+    u64 multi_min = 1ull << 31;
     std::vector<int32_t> node_id, group, parent_rank;
     std::vector<uint8_t> weight;
     bool weights_empty = true; // len(p2pWeights) == 0
@@ -251,9 +297,10 @@ bool build_plan(const tp_policy *p, Prep &out) {
     // Kernel TRI pays more per item (it builds its lane registers per walked prefix, and an item that
     // covers only part of a prefix runs the generic pass), so its items are larger: the longest one
     // (the heaviest run first) about 45 % of what a warp has to do in the whole search.  Measured on 8 of 64:
-    // 0.400 ms at 4 K, 0.352 at 11 K, 0.314 at 64 K, 0.449 at 128 K subsets per lane and item.
+    // 0.400 ms at 4 K, 0.352 at 11 K, 0.314 at 64 K, 0.449 at 128 K subsets per lane and item; slowest of
+    // 8 shards of 8 of 80: 0.289 ms at 8 K, 0.255 at 32 K, 0.333 at 48 K.
     if (tri_gcap > 0 && !out.batch)
-        cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (72000ull * (u64)std::max(out.shards, 1))), 262144);
+        cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (110000ull * (u64)std::max(out.shards, 1))), 262144);
     if (p->tune_cap) cap0 = std::max<u64>(64, p->tune_cap); // tuning aid
     // Single values of b0 become items of their own, cut by b1 (D >= 2 only) -- only where it matters:
     // when one value alone is more than a quarter of what a lane has to do in this search (shard);
@@ -597,6 +644,69 @@ int run_search(tp_policy *p, Ctx &c, const Prep &pr, int shard_idx, int shard_cn
     return 0;
 }
 
+// One request on all of the policy's GPUs: shard s of N runs on GPU s (N = 1 + extra GPUs), each GPU driven by
+// its own thread (the caller's for the first one), every shard's packed winner comes back to the host, the
+// minimum wins.  The shards are the ones tp_search_shard hands out, so the result is that of one GPU.
+int allocate_multi(tp_policy *p, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
+                   int32_t *out, tp_result *info) {
+    const int N = 1 + (int)p->peers.size();
+    Prep pr;
+    prepare(p, avail, n_avail, req, n_req, size, pr, N); // the work plan sized for N shards
+    if (pr.status) return pr.status;
+    std::vector<TpKey> keys(N, TpKey{TP_KEY_INF_HI, TP_KEY_INF_HI});
+    std::vector<tp_result> infos(N);
+    std::vector<int> rcs(N, 0);
+    std::mutex mu;
+    std::condition_variable cv;
+    int pending = N - 1;
+    auto shard = [&](tp_policy *q, int s) {
+        DeviceGuard guard(q->cuda_device);
+        CtxLease lease(q);
+        memset(&infos[s], 0, sizeof(tp_result));
+        rcs[s] = run_search(q, lease.ctx(), pr, s, N, 1, true, &keys[s], &infos[s], nullptr);
+    };
+    for (int s = 1; s < N; s++)
+        p->workers[s - 1]->submit([&, s] {
+            shard(p->peers[s - 1], s);
+            std::lock_guard<std::mutex> lk(mu);
+            if (--pending == 0) cv.notify_one();
+        });
+    shard(p, 0);
+    {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return pending == 0; });
+    }
+    TpKey key{TP_KEY_INF_HI, TP_KEY_INF_HI};
+    tp_result sum{};
+    for (int s = 0; s < N; s++) {
+        if (rcs[s]) {
+            if (s > 0 && rcs[s] == TP_ERR_CUDA) { // the text lives in the peer's handle: bring it home
+                std::lock_guard<std::mutex> lk(p->mu);
+                p->last_cuda_error = "GPU " + std::to_string(p->peers[s - 1]->cuda_device) + ": " +
+                                     p->peers[s - 1]->last_cuda_error;
+            }
+            return rcs[s];
+        }
+        if (tp_key_less(keys[s], key)) key = keys[s];
+        sum.subsets_scored += infos[s].subsets_scored;
+        sum.gpu_launches += infos[s].gpu_launches;
+        sum.kernel_ms = std::max(sum.kernel_ms, infos[s].kernel_ms);
+    }
+    if (info) {
+        *info = sum;
+        info->searched = 1;
+        info->kernel = pr.kernel;
+        info->subsets_total = pr.rq.total;
+        info->key.hi = key.hi;
+        info->key.lo = key.lo;
+        if (key.hi != TP_KEY_INF_HI) {
+            info->score = tp_key_score(key);
+            info->groups_touched = tp_key_groups(key);
+        }
+    }
+    return decode(pr, key, req, out);
+}
+
 } // namespace
 
 extern "C" {
@@ -618,7 +728,6 @@ const char *tp_strerror(int status) {
     case TP_ERR_STATIC_SCRATCH:
         return "request does not fit the static scratch (more than 2^38 subsets, or size minus required above 16)";
     case TP_ERR_CUDA: return "CUDA error";
-    case TP_ERR_NCCL: return "NCCL error";
     }
     return "unknown status";
 }
@@ -694,12 +803,33 @@ int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
         tp_destroy(p);
         return rc;
     }
+    // the other GPUs: a complete single-GPU policy each (same topology, same tuning), and its worker thread
+    const int extra = o ? o->n_extra_devices : 0;
+    if (extra < 0 || extra > TP_MAX_GPUS) { tp_destroy(p); return TP_ERR_BAD_ARGUMENT; }
+    if (o && o->multi_gpu_min_subsets) p->multi_min = o->multi_gpu_min_subsets;
+    for (int i = 0; i < extra; i++) {
+        const int d = o->extra_devices[i];
+        if (d < 0) { tp_destroy(p); return TP_ERR_BAD_ARGUMENT; }
+        tp_options o2 = *o;
+        o2.cuda_device = d;
+        o2.n_extra_devices = 0;
+        tp_policy *peer = nullptr;
+        rc = tp_create(t, &o2, &peer);
+        if (rc) { // e.g. an ordinal that does not exist: Init fails, the plugin runs without the policy
+            tp_destroy(p);
+            return rc;
+        }
+        p->peers.push_back(peer);
+        p->workers.push_back(new GpuWorker());
+    }
     *out = p;
     return TP_OK;
 }
 
 void tp_destroy(tp_policy *p) {
     if (!p) return;
+    for (GpuWorker *w : p->workers) delete w; // (joins: no shard is in flight any more)
+    for (tp_policy *q : p->peers) tp_destroy(q);
     if (p->host_only) {
         delete p;
         return;
@@ -724,6 +854,8 @@ int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32
     if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; } // :110-112, as given
     if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }   // :114-116
     if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
+    if (!p->peers.empty() && !pr.family_only && pr.kernel != TP_KERNEL_FAMILY && pr.rq.total >= p->multi_min)
+        return allocate_multi(p, avail, n_avail, req, n_req, size, out, info);
     DeviceGuard guard(p->cuda_device);
     CtxLease lease(p);
     TpKey key;
