@@ -101,7 +101,7 @@ class ClockSampler:
 def ncu_dram_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the search kernel, from the
     committed `ncu --set full` summary of this round (profiles/); None when there is none."""
-    name = {1: "r1_lex_ncu_full.txt", 2: "r1_split_final_c4_ncu_full.txt"}.get(kernel)
+    name = {1: "r1_lex_ncu_full.txt", 2: "r1_split_final_c4_ncu_full.txt", 4: "r2_tri_final_c4_ncu_full.txt"}.get(kernel)
     path = os.path.join(ROOT, "profiles", name) if name else None
     if not path or not os.path.exists(path):
         return None
@@ -203,8 +203,10 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the search has no CPU path")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        cpu_group = dist.new_group(backend="gloo")  # handle exchange and waits that must not occupy a GPU
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run"
 
     devs, pairs, ids, req, size, expected, score = workload()
@@ -231,10 +233,25 @@ def main():
     stream = torch.cuda.current_stream()
     launches = 0
 
+    # The path's one exchange step -- the min of the shards' packed (score, RefKey) winners -- is fused into
+    # the search kernel (its last block stores the winner into every rank's buffer over NVLink and waits for
+    # the others'); the NCCL min-all-reduce it replaces is timed further down for comparison.
+    exchange = None
+    if world > 1:
+        def gather_handles(raw):
+            got = [None] * world
+            dist.all_gather_object(got, raw, group=cpu_group)
+            return got
+        exchange = tp.Exchange(pol, rank, world, gather_handles)
+
     def step():
+        if exchange is not None:
+            return prep.launch_exchange(exchange, stream.cuda_stream, out.data_ptr())
+        return prep.launch(stream.cuda_stream, out.data_ptr())
+
+    def step_nccl():
         n = prep.launch(stream.cuda_stream, out.data_ptr())
-        if world > 1:  # the path's one exchange step: min of the packed (score, RefKey) winner
-            dist.all_reduce(out[0:1], op=dist.ReduceOp.MIN)
+        dist.all_reduce(out[0:1], op=dist.ReduceOp.MIN)
         return n
 
     sampler = ClockSampler(local_rank)
@@ -263,25 +280,29 @@ def main():
     if clocks is not None:
         clocks["sampled_over"] = f"warm-up + {args.steps} timed steps + {sustain} untimed steps of the same search ({sustain_ms:.0f} ms)"
     key_hi = int(out[0].item())
-    scored = torch.tensor([int(out[2].item())], dtype=torch.int64, device=dev)
-    if world > 1:
-        dist.all_reduce(scored)
-    total_subsets = int(scored.item())
+    total_subsets = int(out[2].item())  # (with the fused exchange: already the sum over the ranks)
     got = pol.Decode(ids, req, size, (key_hi, 0))
     assert got == expected and (key_hi >> 40) == score, (got, key_hi)
     assert total_subsets == 28987537150, total_subsets
     value = total_subsets * args.steps / (dev_ms * 1e-3)
 
     # ---- e2e: the reference-facing call, host buffers in, host ids out -------------------
-    h2d, d2h = 672, 24  # sizeof(TpReq) up, key + count down (csrc/tp_common.cuh, tp_abi.cu)
+    h2d, d2h = tp.lib().tp_descriptor_bytes(0), 24  # the prepared request up, key + count down
+
+    e2e_out = torch.zeros(3, dtype=torch.int64, device=dev)
+    e2e_host = torch.zeros(3, dtype=torch.int64).pin_memory()
 
     def e2e_step():
         if world == 1:
             return pol.Allocate(ids, req, size)
-        key = pol.SearchShard(ids, req, size, rank, world)
-        t = torch.tensor([key[0]], dtype=torch.int64).pin_memory().to(dev, non_blocking=True)
-        dist.all_reduce(t, op=dist.ReduceOp.MIN)
-        return pol.Decode(ids, req, size, (int(t.item()), 0))
+        # every rank: validate + upload the request (H2D), search its shard with the fused exchange, read the
+        # global winner back (D2H), decode it to ids
+        q = tp.PreparedSearch(pol, ids, req, size, shard_index=rank, shard_count=world)
+        q.launch_exchange(exchange, stream.cuda_stream, e2e_out.data_ptr())
+        e2e_host.copy_(e2e_out, non_blocking=True)
+        stream.synchronize()
+        q.close()
+        return pol.Decode(ids, req, size, (int(e2e_host[0]), int(e2e_host[1])))
 
     for _ in range(min(args.warmup, 2)):
         e2e_step()
@@ -293,8 +314,41 @@ def main():
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     assert res == expected
     e2e_value = 28987537150 * args.steps / e2e_s
+
+    # ---- A/B of the exchange (untimed for the headline): kernel + NCCL min-all-reduce -----------
+    exchange_ab = None
     if world > 1:
-        h2d, d2h = h2d + 8, d2h + 8
+        for _ in range(3):
+            step_nccl()
+        barrier()
+        ab = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+        for e0, e1 in ab:
+            flush.fill_(1)
+            e0.record(stream)
+            step_nccl()
+            e1.record(stream)
+        barrier()
+        nccl_ms = max_over_ranks(sum(e0.elapsed_time(e1) for e0, e1 in ab)) / args.steps
+        exchange_ab = {"fused_in_kernel_ms_per_step": dev_ms / args.steps, "kernel_plus_nccl_allreduce_ms_per_step": nccl_ms}
+
+    # ---- one process, one call, all GPUs (what a Go plugin can do: it cannot torchrun) -----------
+    single_process = None
+    if world > 1:
+        if rank == 0:
+            mp = tp.BestEffortPolicy(cuda_device=0, extra_devices=list(range(1, world)))
+            mp.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
+            for _ in range(3):
+                assert mp.Allocate(ids, req, size) == expected
+            t1 = time.perf_counter()
+            for _ in range(args.steps):
+                mp.Allocate(ids, req, size)
+            dt = (time.perf_counter() - t1) / args.steps
+            single_process = {"what": "BestEffortPolicy.Allocate of ONE process on all GPUs (tp_options.extra_devices): "
+                                      "host ids in, host ids out, shards launched by per-GPU threads, host-side min",
+                              "n_gpus": world, "ms_per_call": dt * 1e3, "subsets_per_s": 28987537150 / dt,
+                              "kernel_ms_slowest_gpu": mp.last["kernel_ms"], "gpu_launches": mp.last["gpu_launches"]}
+            mp.close()
+        dist.barrier(group=cpu_group)  # the other ranks wait on the CPU: their GPUs are rank 0's for this leg
 
     line = None
     if rank == 0:
@@ -303,15 +357,17 @@ def main():
                                            shard_count=world)
         k_ms /= max(args.steps, 3)
         shard_subsets = prep.subsets
-        if info["kernel"] == tp.KERNEL_SPLIT:
-            h2d += 1176  # the work plan (TpPlan) travels with the request descriptor
+        packed = info["kernel"] in (tp.KERNEL_SPLIT, tp.KERNEL_TRI)
+        if packed:
+            h2d = tp.lib().tp_descriptor_bytes(1)  # the work plan (TpPlan) travels with the request descriptor
         peak_iadd = tp.measure_int_peak(local_rank, 0)      # IADD3, 32-bit lane-ops/s (x1e9)
         peak_addmin = tp.measure_int_peak(local_rank, 3)    # VIADDMNMX.U16x2 lane-instr/s (x1e9)
         rate = shard_subsets / (k_ms * 1e-3)
-        if info["kernel"] == tp.KERNEL_SPLIT:
-            # SPLIT executes one 16-bit add and one 16-bit min per subset (VIADDMNMX.U16x2: two
+        if packed:
+            # TRI and SPLIT execute one 16-bit add and one 16-bit min per subset (VIADDMNMX.U16x2: two
             # subsets per lane-instruction); the peak is that instruction's measured rate x 4 ops.
-            ops_per_subset, kname, unit_note = 2, "tp_exhaustive_split<80,2>", "16-bit integer add/min ops"
+            ops_per_subset, unit_note = 2, "16-bit integer add/min ops"
+            kname = "tp_exhaustive_tri<80,1>" if info["kernel"] == tp.KERNEL_TRI else "tp_exhaustive_split<80,2>"
             peak_tops = peak_addmin * 4 / 1e3
             peak_src = "VIADDMNMX.U16x2 microbenchmark in this run (tp_measure_int_peak variant 3) x 4 ops/lane-instr"
         else:
@@ -331,12 +387,16 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None,
-                "dtype": "u16" if info["kernel"] == tp.KERNEL_SPLIT else "int32", "data": "synthetic",
+                "dtype": "u16" if packed else "int32", "data": "synthetic",
                 "config": bench_config(world),
                 "clocks": clocks,
                 "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                         "ms_per_step": e2e_s / args.steps * 1e3, "api": "BestEffortPolicy.Allocate(ids, req, size)"},
                 "gpu_launches": launches, "roofline": roofline}
+        if exchange_ab:
+            line["exchange_ab"] = exchange_ab
+        if single_process:
+            line["single_process_multi_gpu"] = single_process
         if world == 1 and not args.no_extra:
             line["latency"] = latency_leg(tp, dev)
             line["c3"] = c3_leg(tp, peak_addmin)
@@ -359,6 +419,8 @@ def main():
                                     "sample": f"ranks [0, {n}) of C(80,8) in {dt:.1f}s, oracle/exhaustive.c, "
                                               f"{os.cpu_count()} host cpus visible"}
     prep.close()
+    if exchange is not None:
+        exchange.close()
     pol.close()
     if world > 1:
         dist.barrier()

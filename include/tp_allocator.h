@@ -196,6 +196,26 @@ uint64_t tp_prepared_subsets(const tp_prepared *q); /* subsets this shard scores
 void tp_prepared_free(tp_policy *p, tp_prepared *q);
 
 /*
+ * Multi-process runs (one process per GPU, e.g. under torch.distributed.run): the exchange of the shards'
+ * winners fused into the search kernel instead of a collective launched behind it.  (No counterpart in the
+ * reference; the single-process form of the same thing is tp_options.extra_devices.)  Every rank
+ *   1. tp_exchange_create  -- a small buffer in its GPU's memory, exported as a CUDA IPC handle (64 bytes),
+ *   2. gathers all ranks' handles by whatever means it has (a host all-gather),
+ *   3. tp_exchange_connect -- maps the other ranks' buffers (peer access over NVLink),
+ * and then launches with tp_launch_exchange instead of tp_launch: the kernel's last block stores its shard's
+ * packed winner into every rank's buffer and waits for the others', so that d_out holds the GLOBAL minimum
+ * (and the global count of subsets scored) on every rank when the kernel ends.  All ranks must make the same
+ * sequence of tp_launch_exchange calls (an exchange is matched by its sequence number).  A rank that never
+ * arrives makes the others give up after 5 s with TP_KEY_NONE in d_out[0].
+ */
+#define TP_IPC_HANDLE_BYTES 64
+typedef struct tp_exchange tp_exchange;
+int tp_exchange_create(tp_policy *p, int32_t rank, int32_t world, tp_exchange **out, void *handle_out /* 64 bytes */);
+int tp_exchange_connect(tp_exchange *x, const void *handles /* world x 64 bytes, rank order */);
+int tp_launch_exchange(tp_policy *p, tp_prepared *q, tp_exchange *x, void *cuda_stream, uint64_t *d_out);
+void tp_exchange_destroy(tp_exchange *x);
+
+/*
  * tp_allocate without a tp_policy and without creating any memory.  (This entry point has no
  * counterpart in the reference: the Go policy never leaves the host heap.)
  *
@@ -228,6 +248,10 @@ void tp_prepared_free(tp_policy *p, tp_prepared *q);
 int tp_allocate_static(const tp_topology *topo, const uint8_t *d_weight, const int32_t *available,
                        int32_t n_available, const int32_t *required, int32_t n_required, int32_t size,
                        void *cuda_stream, uint64_t *d_out, int32_t *out, tp_result *info);
+
+/* Bytes of the prepared request a search uploads to the GPU (with_plan: plus the work plan of the SPLIT / TRI
+ * kernels): what bench.py counts as host-to-device traffic per request.  The way back is 24 bytes. */
+int tp_descriptor_bytes(int32_t with_plan);
 
 /* Development hook (tests, tuning sweeps; no counterpart in the reference): override the work plan of the
  * exhaustive kernels for requests prepared after the call -- walk_q = positions below the lane set (forces

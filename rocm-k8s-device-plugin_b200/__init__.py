@@ -131,6 +131,11 @@ def lib() -> C.CDLL:
     L.tp_prepared_free.argtypes = [C.c_void_p, C.c_void_p]
     L.tp_prepared_free.restype = None
     L.tp_measure_int_peak.argtypes = [C.c_int32, C.c_int32, C.POINTER(C.c_double)]
+    L.tp_exchange_create.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_void_p), C.c_char_p]
+    L.tp_exchange_connect.argtypes = [C.c_void_p, C.c_char_p]
+    L.tp_launch_exchange.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.tp_exchange_destroy.argtypes = [C.c_void_p]
+    L.tp_exchange_destroy.restype = None
     L.tp_set_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64]
     L.tp_set_tuning.restype = None
     L.tp_allocate_static.argtypes = [C.POINTER(TpTopology), C.c_void_p, I32P, C.c_int32, I32P, C.c_int32,
@@ -355,10 +360,43 @@ class PreparedSearch:
             raise AllocatorError(rc, strerror(rc) + ": " + lib().tp_last_cuda_error(self._pol.handle).decode())
         return rc
 
+    def launch_exchange(self, exchange, cuda_stream: int, d_out_ptr: int) -> int:
+        """tp_launch_exchange: as launch(), but d_out receives the minimum over ALL ranks' shards (and the
+        sum of their counts): the exchange is fused into the kernel's last block."""
+        rc = lib().tp_launch_exchange(self._pol.handle, self._q, exchange._x, C.c_void_p(cuda_stream),
+                                      C.c_void_p(d_out_ptr))
+        if rc < 0:
+            raise AllocatorError(rc, strerror(rc) + ": " + lib().tp_last_cuda_error(self._pol.handle).decode())
+        return rc
+
     def close(self):
         if getattr(self, "_q", None):
             lib().tp_prepared_free(self._pol.handle, self._q)
             self._q = None
+
+    __del__ = close
+
+
+class Exchange:
+    """tp_exchange_*: the fused winner exchange of a multi-process run.  `all_gather(handle_bytes)` must
+    return every rank's 64-byte handle in rank order (e.g. through torch.distributed.all_gather_object)."""
+
+    def __init__(self, pol: BestEffortPolicy, rank: int, world: int, all_gather):
+        self._x = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        rc = lib().tp_exchange_create(pol.handle, rank, world, C.byref(self._x), handle)
+        if rc < 0:
+            raise AllocatorError(rc, strerror(rc) + ": " + lib().tp_last_cuda_error(pol.handle).decode())
+        handles = all_gather(handle.raw)
+        assert len(handles) == world and all(len(h) == 64 for h in handles)
+        rc = lib().tp_exchange_connect(self._x, b"".join(handles))
+        if rc < 0:
+            raise AllocatorError(rc, "tp_exchange_connect: " + strerror(rc))
+
+    def close(self):
+        if getattr(self, "_x", None):
+            lib().tp_exchange_destroy(self._x)
+            self._x = None
 
     __del__ = close
 

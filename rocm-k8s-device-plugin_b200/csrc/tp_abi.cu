@@ -1251,6 +1251,89 @@ int tp_launch(tp_policy *p, tp_prepared *q, void *cuda_stream, uint64_t *d_out) 
     return li.launches;
 }
 
+struct tp_exchange {
+    int device = 0, rank = 0, world = 0;
+    unsigned long long *local = nullptr;          // [2][world][TP_EX_SLOT_WORDS]
+    unsigned long long *peer[TP_MAX_GPUS] = {};   // local for `rank`, IPC mappings for the others
+    bool connected = false;
+    unsigned long long epoch = 0;
+};
+
+int tp_exchange_create(tp_policy *p, int32_t rank, int32_t world, tp_exchange **out, void *handle_out) {
+    if (!p || !out || !handle_out || world < 1 || world > TP_MAX_GPUS || rank < 0 || rank >= world) return TP_ERR_BAD_ARGUMENT;
+    if (p->host_only) return TP_ERR_CUDA;
+    static_assert(sizeof(cudaIpcMemHandle_t) == TP_IPC_HANDLE_BYTES, "IPC handle size");
+    tp_exchange *x = new (std::nothrow) tp_exchange();
+    if (!x) return TP_ERR_BAD_ARGUMENT;
+    x->device = p->cuda_device;
+    x->rank = rank;
+    x->world = world;
+    DeviceGuard guard(x->device);
+    const size_t bytes = (size_t)2 * world * TP_EX_SLOT_WORDS * sizeof(unsigned long long);
+    cudaIpcMemHandle_t h;
+    cudaError_t e = cudaMalloc((void **)&x->local, bytes);
+    if (e == cudaSuccess) e = cudaMemset(x->local, 0, bytes);
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, x->local);
+    if (e != cudaSuccess) {
+        if (x->local) cudaFree(x->local);
+        delete x;
+        std::lock_guard<std::mutex> lk(p->mu);
+        p->last_cuda_error = std::string("tp_exchange_create: ") + cudaGetErrorString(e);
+        return TP_ERR_CUDA;
+    }
+    memcpy(handle_out, &h, sizeof h);
+    x->peer[rank] = x->local;
+    *out = x;
+    return TP_OK;
+}
+
+int tp_exchange_connect(tp_exchange *x, const void *handles) {
+    if (!x || !handles) return TP_ERR_BAD_ARGUMENT;
+    DeviceGuard guard(x->device);
+    for (int r = 0; r < x->world; r++) {
+        if (r == x->rank || x->peer[r]) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, (const unsigned char *)handles + (size_t)r * TP_IPC_HANDLE_BYTES, sizeof h);
+        void *ptr = nullptr;
+        if (cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) return TP_ERR_CUDA;
+        x->peer[r] = (unsigned long long *)ptr;
+    }
+    x->connected = true;
+    return TP_OK;
+}
+
+void tp_exchange_destroy(tp_exchange *x) {
+    if (!x) return;
+    DeviceGuard guard(x->device);
+    for (int r = 0; r < x->world; r++)
+        if (r != x->rank && x->peer[r]) cudaIpcCloseMemHandle(x->peer[r]);
+    if (x->local) cudaFree(x->local);
+    delete x;
+}
+
+int tp_launch_exchange(tp_policy *p, tp_prepared *q, tp_exchange *x, void *cuda_stream, uint64_t *d_out) {
+    if (!p || !q || !x || !d_out || !x->connected || x->world != q->shard_count || x->rank != q->shard_index)
+        return TP_ERR_BAD_ARGUMENT;
+    Ctx &c = p->ctxs[q->ctx_idx];
+    DeviceGuard guard(p->cuda_device);
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    TpScratch sc = c.scratch;
+    sc.out = (TpKey *)d_out;
+    sc.out_scored = (u64 *)(d_out + 2);
+    for (int r = 0; r < x->world; r++) sc.ex.peer[r] = x->peer[r];
+    sc.ex.rank = x->rank;
+    sc.ex.world = x->world;
+    sc.ex.epoch = ++x->epoch;
+    TpLaunchInfo li{};
+    if (!shard_nonempty(q->pr, q->shard_index, q->shard_count)) {
+        // a shard without work still has to show up in the exchange: one block of the LEX kernel over an empty range
+        TP_CUDA(p, tp_launch_exchange_only(sc, st));
+        return 1;
+    }
+    TP_CUDA(p, launch_search(p, c, q->pr, q->shard_index, q->shard_count, sc, st, &li));
+    return li.launches;
+}
+
 uint64_t tp_prepared_subsets(const tp_prepared *q) { return q ? q->subsets : 0; }
 
 void tp_prepared_free(tp_policy *p, tp_prepared *q) {
@@ -1330,6 +1413,8 @@ int tp_allocate_static(const tp_topology *t, const uint8_t *d_weight, const int3
     }
     return decode(pr, key, req, out);
 }
+
+int tp_descriptor_bytes(int32_t with_plan) { return (int)(sizeof(TpReq) + (with_plan ? sizeof(TpPlan) : 0)); }
 
 void tp_set_tuning(tp_policy *p, int32_t walk_q, uint64_t item_cap, uint64_t item_cap1) {
     if (!p) return;

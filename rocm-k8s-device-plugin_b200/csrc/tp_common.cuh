@@ -85,12 +85,27 @@ __host__ __device__ __forceinline__ int tp_key_groups(const TpKey &k) { return (
 
 // Per-launch scratch in global memory: one partial winner per block, reduced by the
 // last block to finish (ticket), so one launch yields the final key with no second kernel.
+// Winner exchange between the ranks of a multi-process run (one process per GPU), fused into the
+// search kernel's last block: it stores (key, count, epoch) into slot [epoch & 1][rank] of EVERY
+// rank's buffer -- plain st.global through peer mappings (CUDA IPC), 32 bytes per peer over NVLink --
+// then waits until the `world` slots of its own buffer carry this epoch and takes their minimum,
+// so that every rank's kernel ends with the global winner and no collective kernel follows.
+// Two slots per rank (epoch parity): a rank cannot be two exchanges ahead of another, since it
+// leaves an exchange only after all ranks have published for it.  world == 0: no exchange.
+#define TP_EX_SLOT_WORDS 4 /* key.hi, key.lo, subsets scored, epoch (written last) */
+struct TpExchangeDev {
+    unsigned long long *peer[TP_MAX_GPUS]; // every rank's buffer, own included: [2][world][TP_EX_SLOT_WORDS]
+    int rank, world;
+    unsigned long long epoch; // > 0, the same on all ranks for one exchange
+};
+
 struct TpScratch {
     TpKey *partial;               // [max_blocks]
     unsigned long long *scored;   // running count of subsets scored
     unsigned int *ticket;         // blocks finished
     TpKey *out;                   // final key
     unsigned long long *out_scored;
+    TpExchangeDev ex;
 };
 
 #define TP_MAX_BLOCKS 4096

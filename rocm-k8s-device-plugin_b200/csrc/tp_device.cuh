@@ -129,9 +129,51 @@ static __device__ bool tp_block_finish(TpKey best, u64 counted, const TpScratch 
         TpKey f = {TP_KEY_INF_HI, TP_KEY_INF_HI};
         if (lane < nwarps) f = s_red[lane];
         f = tp_warp_min_key(f);
+        u64 total = 0;
+        if (lane == 0) total = atomicExch(sc.scored, 0ull);
+        if (sc.ex.world > 1) { // fused exchange (see TpExchangeDev): lane r talks to rank r
+            f.hi = __shfl_sync(0xFFFFFFFFu, f.hi, 0);
+            f.lo = __shfl_sync(0xFFFFFFFFu, f.lo, 0);
+            total = __shfl_sync(0xFFFFFFFFu, total, 0);
+            const int world = sc.ex.world;
+            const size_t base = (size_t)(sc.ex.epoch & 1) * world;
+            TpKey k = {TP_KEY_INF_HI, TP_KEY_INF_HI};
+            u64 c = 0;
+            if (lane < world) {
+                volatile u64 *dst = sc.ex.peer[lane] + (base + sc.ex.rank) * TP_EX_SLOT_WORDS;
+                dst[0] = f.hi;
+                dst[1] = f.lo;
+                dst[2] = total;
+                __threadfence_system();
+                dst[3] = sc.ex.epoch;
+                volatile u64 *src = sc.ex.peer[sc.ex.rank] + (base + lane) * TP_EX_SLOT_WORDS;
+                u64 t0, t1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+                bool ok = true;
+                while (src[3] != sc.ex.epoch) { // a rank that never publishes must not hang the others
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                    if (t1 - t0 > 5000000000ull) { // 5 s
+                        ok = false;
+                        break;
+                    }
+                }
+                __threadfence_system();
+                if (ok) {
+                    k.hi = src[0];
+                    k.lo = src[1];
+                    c = src[2];
+                } else {
+                    c = ~0ull >> 1; // poison: the count can no longer add up
+                }
+            }
+            f = tp_warp_min_key(k);
+#pragma unroll
+            for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, off);
+            total = c;
+        }
         if (lane == 0) {
             *sc.out = f;
-            *sc.out_scored = atomicExch(sc.scored, 0ull);
+            *sc.out_scored = total;
             *sc.ticket = 0u;
         }
     }

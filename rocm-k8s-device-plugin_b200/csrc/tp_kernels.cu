@@ -412,6 +412,15 @@ cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const u64 *
     return cudaGetLastError();
 }
 
+__global__ void tp_exchange_only_kernel(TpScratch sc) {
+    tp_block_finish(TpKey{TP_KEY_INF_HI, TP_KEY_INF_HI}, 0ull, sc);
+}
+
+cudaError_t tp_launch_exchange_only(const TpScratch &sc, cudaStream_t st) {
+    tp_exchange_only_kernel<<<1, 32, 0, st>>>(sc);
+    return cudaGetLastError();
+}
+
 // Kernel SPLIT: pick the narrowest lane vector that holds every pivot (n - p positions).
 static cudaError_t tp_dispatch_split(int D, int need, const uint8_t *d_weight, int n_devices, const u64 *d_binom,
                                      const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int shard_idx,
@@ -714,7 +723,7 @@ cudaError_t tp_launch_exhaustive_lex_static(const uint8_t *d_weight, int n_devic
     if (e != cudaSuccess) return e;
     e = cudaMemcpyAsync(base + TP_STATIC_OFF_REQ, &h_rq, sizeof(TpReq), cudaMemcpyHostToDevice, st);
     if (e != cudaSuccess) return e;
-    TpScratch sc;
+    TpScratch sc{};
     sc.partial = (TpKey *)(base + TP_STATIC_OFF_PARTIAL);
     sc.scored = (u64 *)(base + TP_STATIC_OFF_WORDS);
     sc.ticket = (unsigned int *)(base + TP_STATIC_OFF_WORDS + 8);

@@ -93,6 +93,9 @@ cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const unsig
                              unsigned long long mask_hi, const TpScratch &scratch, int sm_count,
                              cudaStream_t stream, TpLaunchInfo *info);
 
+// A rank whose shard is empty still takes part in the fused exchange (TpExchangeDev): "no candidate, nothing scored".
+cudaError_t tp_launch_exchange_only(const TpScratch &scratch, cudaStream_t stream);
+
 cudaError_t tp_launch_build_weights(int n, const int32_t *d_group, const int32_t *d_numa, const int32_t *d_link,
                                     uint8_t *d_out, cudaStream_t stream);
 
