@@ -482,7 +482,16 @@ def latency_leg(tp, dev):
         # timed device-resident through the regular multi-block launch (an upper bound for its kernel)
         tp.search_resident(pol, ids, [], size, iters=3)  # first launch of an instantiation loads its code
         k_ms, _, _ = tp.search_resident(pol, ids, [], size, iters=200)
-        out[name] = {"subsets": info["subsets_total"], "c_abi_p50_us": percentile(abi, 50),
+        native = None
+        try:  # the same request from a native caller: no interpreter, no GIL (SURVEY 8(d) latency protocol)
+            sys.path.insert(0, os.path.join(ROOT, "tests", "harness"))
+            import run_harness
+            run_harness.build()
+            native = run_harness.run(name, devs, pairs, ids, [], size)
+            assert native["mismatches"] == 0
+        except Exception as e:  # the harness is tooling: its absence must not take the bench line down
+            native = {"unavailable": repr(e)[:200]}
+        out[name] = {"native": native, "subsets": info["subsets_total"], "c_abi_p50_us": percentile(abi, 50),
                      "c_abi_mean_us": sum(abi) / len(abi), "kernel_events_us": k_ms / 200 * 1e3,
                      "concurrent8_p50_us": percentile(conc_all, 50), "concurrent8_p99_us": percentile(conc_all, 99),
                      "concurrent8_calls_per_s": len(conc_all) / conc_s,
@@ -491,7 +500,9 @@ def latency_leg(tp, dev):
                      "cpu_reference_bfs_p50_us": percentile(cpu, 50),
                      "cpu_reference_candidates": ref.last["n_candidates"]}
         pol.close()
-    out["note"] = "wall clock around the call (python ctypes overhead included in all three columns)"
+    out["note"] = ("python columns: wall clock around the ctypes call (interpreter overhead included, concurrent callers share the "
+                   "GIL); `native`: tests/harness/abi_harness.cpp, clock_gettime(CLOCK_MONOTONIC) around tp_allocate from C++ "
+                   "threads -- the numbers a cgo caller would see")
     return out
 
 

@@ -66,7 +66,8 @@ def build(force=False, verbose=False):
         logs = list(ex.map(lambda s: _compile(s, force, verbose), SOURCES))
     if verbose:
         print("\n".join(logs))
-    cmd = ["nvcc", "-shared", "-cudart", "static"] + ARCH + ["-o", LIB] + [_obj(s) for s in SOURCES]
+    cmd = (["nvcc", "-shared", "-cudart", "static"] + ARCH + os.environ.get("TP_BUILD_LDFLAGS", "").split() +
+           ["-o", LIB] + [_obj(s) for s in SOURCES])
     subprocess.run(cmd, check=True, cwd=CSRC)
     return LIB
 

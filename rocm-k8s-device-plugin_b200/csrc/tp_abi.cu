@@ -357,10 +357,11 @@ void prepare(const tp_policy *p, const int32_t *avail, int n_avail, const int32_
     if (n_req > size) { out.status = TP_ERR_INVALID_REQUIRED; return; }            // :98-100
     if (n_req > n_avail) { out.status = TP_ERR_INVALID_REQ_AVAILABLE; return; }    // :102-104
     if (p->n == 0) { out.status = TP_ERR_INVALID_INIT; return; }                   // :106-108
+    // (a NULL array with a positive count would be read by the short-circuits' copies: refuse it first)
+    if ((n_avail > 0 && !avail) || (n_req > 0 && !req)) { out.status = TP_ERR_BAD_ARGUMENT; return; }
     if (n_avail == size) { out.shortcut = 1; return; }                             // :110-112
     if (n_req == size) { out.shortcut = 2; return; }                               // :114-116
     if (p->weights_empty) { out.status = TP_ERR_INVALID_INIT; return; }            // :118-120
-    if ((n_avail > 0 && !avail) || (n_req > 0 && !req)) { out.status = TP_ERR_BAD_ARGUMENT; return; }
 
     // setContainsAll (:122-124) is evaluated on ids before any lookup; an index outside
     // the policy is an id the reference's devicesMap does not know (it would nil-deref).
@@ -647,12 +648,8 @@ int run_search(tp_policy *p, Ctx &c, const Prep &pr, int shard_idx, int shard_cn
 // One request on all of the policy's GPUs: shard s of N runs on GPU s (N = 1 + extra GPUs), each GPU driven by
 // its own thread (the caller's for the first one), every shard's packed winner comes back to the host, the
 // minimum wins.  The shards are the ones tp_search_shard hands out, so the result is that of one GPU.
-int allocate_multi(tp_policy *p, const int32_t *avail, int n_avail, const int32_t *req, int n_req, int size,
-                   int32_t *out, tp_result *info) {
-    const int N = 1 + (int)p->peers.size();
-    Prep pr;
-    prepare(p, avail, n_avail, req, n_req, size, pr, N); // the work plan sized for N shards
-    if (pr.status) return pr.status;
+int allocate_multi(tp_policy *p, const Prep &pr, const int32_t *req, int32_t *out, tp_result *info) {
+    const int N = 1 + (int)p->peers.size(); // (pr: prepared with the work plan sized for N shards)
     std::vector<TpKey> keys(N, TpKey{TP_KEY_INF_HI, TP_KEY_INF_HI});
     std::vector<tp_result> infos(N);
     std::vector<int> rcs(N, 0);
@@ -849,13 +846,17 @@ int tp_allocate(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32
     if (!p || !out) return TP_ERR_BAD_ARGUMENT;
     if (info) memset(info, 0, sizeof *info);
     Prep pr;
-    prepare(p, avail, n_avail, req, n_req, size, pr);
+    const int gpus = 1 + (int)p->peers.size();
+    prepare(p, avail, n_avail, req, n_req, size, pr, gpus); // (a multi-GPU policy plans for all its GPUs first)
     if (pr.status) return pr.status;
     if (pr.shortcut == 1) { memcpy(out, avail, sizeof(int32_t) * size); return size; } // :110-112, as given
     if (pr.shortcut == 2) { memcpy(out, req, sizeof(int32_t) * size); return size; }   // :114-116
     if (p->host_only) return TP_ERR_CUDA; // there is no CPU search
-    if (!p->peers.empty() && !pr.family_only && pr.kernel != TP_KERNEL_FAMILY && pr.rq.total >= p->multi_min)
-        return allocate_multi(p, avail, n_avail, req, n_req, size, out, info);
+    if (gpus > 1) {
+        if (!pr.family_only && pr.kernel != TP_KERNEL_FAMILY && pr.rq.total >= p->multi_min)
+            return allocate_multi(p, pr, req, out, info);
+        prepare(p, avail, n_avail, req, n_req, size, pr, 1); // a small search: one GPU, items sized for it
+    }
     DeviceGuard guard(p->cuda_device);
     CtxLease lease(p);
     TpKey key;
@@ -990,6 +991,9 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
             continue;
         }
         if (pr.family_only || pr.kernel == TP_KERNEL_FAMILY) { singles.push_back(i); continue; }
+        // a LEX request gets ONE block in a batch group; a large one (scores beyond the packed kernels' 16-bit
+        // range can hold up to 2^38 subsets) would keep that block, and the whole RPC, busy for minutes
+        if (pr.kernel == TP_KERNEL_LEX && pr.rq.total > (1ull << 24)) { singles.push_back(i); continue; }
         BatchGroup key;
         key.kernel = pr.kernel;
         if (uses_plan(pr.kernel)) {

@@ -233,9 +233,9 @@ Error statusToError(int rc, tp_policy *h) {
 
 std::pair<std::vector<std::string>, Error> BestEffortPolicy::Allocate(const std::vector<std::string> &availableIds,
                                                                       const std::vector<std::string> &requiredIds,
-                                                                      int size) {
+                                                                      int size, tp_result *info) const {
     std::vector<std::string> outset;
-    last_ = tp_result{};
+    if (info) *info = tp_result{};
     // Same checks, same order as besteffort_policy.go:90-124: the count checks and the two
     // short-circuits look at ids only, so they are answered before any id is resolved.
     if (size <= 0) return {outset, kInvalidSize};
@@ -252,7 +252,7 @@ std::pair<std::vector<std::string>, Error> BestEffortPolicy::Allocate(const std:
     mapIds(availableIds, av);
     mapIds(requiredIds, rq);
     std::vector<int32_t> out(size);
-    int rc = tp_allocate(handle_, av.data(), (int)av.size(), rq.data(), (int)rq.size(), size, out.data(), &last_);
+    int rc = tp_allocate(handle_, av.data(), (int)av.size(), rq.data(), (int)rq.size(), size, out.data(), info);
     if (rc < 0) return {outset, statusToError(rc, handle_)};
     for (int i = 0; i < rc; i++) outset.push_back(devices_[out[i]].Id);
     return {outset, ""};
@@ -260,20 +260,20 @@ std::pair<std::vector<std::string>, Error> BestEffortPolicy::Allocate(const std:
 
 Error BestEffortPolicy::SearchShard(const std::vector<std::string> &availableIds,
                                     const std::vector<std::string> &requiredIds, int size, int shardIndex,
-                                    int shardCount, tp_key *key, bool *shortCircuit) {
+                                    int shardCount, tp_key *key, bool *shortCircuit, tp_result *info) const {
     if (!handle_) return kInvalidInit;
     std::vector<int32_t> av, rq;
     mapIds(availableIds, av);
     mapIds(requiredIds, rq);
     int rc = tp_search_shard(handle_, av.data(), (int)av.size(), rq.data(), (int)rq.size(), size, shardIndex,
-                             shardCount, key, &last_);
+                             shardCount, key, info);
     if (shortCircuit) *shortCircuit = rc == 1;
     return statusToError(rc, handle_);
 }
 
 std::pair<std::vector<std::string>, Error> BestEffortPolicy::Decode(const std::vector<std::string> &availableIds,
                                                                     const std::vector<std::string> &requiredIds,
-                                                                    int size, const tp_key &key) {
+                                                                    int size, const tp_key &key) const {
     std::vector<std::string> outset;
     if (!handle_) return {outset, kInvalidInit};
     std::vector<int32_t> av, rq;
@@ -355,8 +355,7 @@ int tph_init_pairs(tph_policy *p, const tph_device *devs, int n, const int32_t *
 
 int tph_allocate(tph_policy *p, const char *const *avail, int n_avail, const char *const *req, int n_req, int size,
                  char *out_ids, tp_result *info) {
-    auto res = p->pol.Allocate(toStrings(avail, n_avail), toStrings(req, n_req), size);
-    if (info) *info = p->pol.LastResult();
+    auto res = p->pol.Allocate(toStrings(avail, n_avail), toStrings(req, n_req), size, info);
     p->last_error = res.second;
     if (!res.second.empty()) return errorToStatus(res.second);
     writeIds(res.first, out_ids);

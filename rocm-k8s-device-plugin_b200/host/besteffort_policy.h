@@ -60,19 +60,27 @@ class BestEffortPolicy : public Policy {
     Error Init(const std::vector<Device> &devs, const std::string &topoDir) override;
     // Init for callers that already hold p2pWeights (the Go parsers stay in Go).
     Error InitWithWeights(const std::vector<Device> &devs, const PairWeights &p2pWeights);
+    // Reentrant, like the reference's (its policy is read-only after Init, one goroutine per RPC calls it):
+    // nothing in the object is written after Init.
     std::pair<std::vector<std::string>, Error> Allocate(const std::vector<std::string> &available,
                                                         const std::vector<std::string> &required,
-                                                        int size) override;
+                                                        int size) override {
+        return Allocate(available, required, size, nullptr);
+    }
+    // The same with the search's counters (score, subsets scored, kernel time) returned to the caller.
+    std::pair<std::vector<std::string>, Error> Allocate(const std::vector<std::string> &available,
+                                                        const std::vector<std::string> &required, int size,
+                                                        tp_result *info) const;
 
     // Shard of the search for multi-GPU runs (tp_search_shard / tp_decode).
     Error SearchShard(const std::vector<std::string> &available, const std::vector<std::string> &required,
-                      int size, int shardIndex, int shardCount, tp_key *key, bool *shortCircuit);
+                      int size, int shardIndex, int shardCount, tp_key *key, bool *shortCircuit,
+                      tp_result *info = nullptr) const;
     std::pair<std::vector<std::string>, Error> Decode(const std::vector<std::string> &available,
                                                       const std::vector<std::string> &required, int size,
-                                                      const tp_key &key);
+                                                      const tp_key &key) const;
 
     void SetOptions(const tp_options &o) { options_ = o; }
-    const tp_result &LastResult() const { return last_; }
     tp_policy *Handle() const { return handle_; }
     size_t WeightRows() const { return p2pWeights_.size(); }
     size_t GroupCount() const { return groupCount_; }
@@ -87,7 +95,6 @@ class BestEffortPolicy : public Policy {
     size_t groupCount_ = 0;
     tp_options options_{};
     tp_policy *handle_ = nullptr;
-    tp_result last_{};
 };
 
 std::unique_ptr<BestEffortPolicy> NewBestEffortPolicy();
