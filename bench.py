@@ -390,13 +390,22 @@ def main():
                 "dtype": "u16" if packed else "int32", "data": "synthetic",
                 "config": bench_config(world),
                 "clocks": clocks,
-                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                        "ms_per_step": e2e_s / args.steps * 1e3, "api": "BestEffortPolicy.Allocate(ids, req, size)"},
+                "e2e": ({"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                         "ms_per_step": e2e_s / args.steps * 1e3, "api": "BestEffortPolicy.Allocate(ids, req, size)"}
+                        if world == 1 else
+                        # N GPUs behind the reference-facing call: ONE process, one Allocate (a Go plugin cannot
+                        # torchrun), every GPU gets the request (H2D) and returns its winner (D2H) inside the call
+                        {"value": single_process["subsets_per_s"], "unit": UNIT, "h2d_bytes_per_step": h2d * world,
+                         "d2h_bytes_per_step": d2h * world, "ms_per_step": single_process["ms_per_call"],
+                         "api": "BestEffortPolicy.Allocate(ids, req, size) of one process over all GPUs "
+                                "(tp_options.extra_devices), timed on rank 0 while the other ranks wait on the CPU"}),
                 "gpu_launches": launches, "roofline": roofline}
         if exchange_ab:
             line["exchange_ab"] = exchange_ab
         if single_process:
             line["single_process_multi_gpu"] = single_process
+            line["e2e_rank_processes"] = {"value": e2e_value, "unit": UNIT, "ms_per_step": e2e_s / args.steps * 1e3,
+                                          "api": "per rank: tp_prepare (H2D) + tp_launch_exchange + D2H of the global winner + tp_decode"}
         if world == 1 and not args.no_extra:
             line["latency"] = latency_leg(tp, dev)
             line["c3"] = c3_leg(tp, peak_addmin)

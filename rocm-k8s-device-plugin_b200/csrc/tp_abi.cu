@@ -963,7 +963,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
     const auto t_start = now();
     std::vector<Prep> preps(n_requests);
     {
-        const unsigned hw = std::max(1u, std::min(16u, std::thread::hardware_concurrency()));
+        const unsigned hw = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
         const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_requests / 64 + 1));
         auto work = [&](int t) {
             for (int i = t; i < n_requests; i += nthreads)
