@@ -548,6 +548,7 @@ u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
 // Enqueue the search kernel chosen by prepare() for shard (idx of cnt) on `st`, result into sc.out.
 cudaError_t launch_search(tp_policy *p, Ctx &c, const Prep &pr, int idx, int cnt, const TpScratch &sc,
                           cudaStream_t st, TpLaunchInfo *li) {
+    (void)cudaGetLastError(); // the launchers report cudaGetLastError(): an older, unrelated error must not be taken for theirs
     if (pr.kernel == TP_KERNEL_TRI)
         return tp_launch_exhaustive_tri(p->d_weight, p->n, p->d_binom, c.d_req, pr.rq, c.d_plan, pr.plan, idx, cnt, sc,
                                         c.d_counter, p->sm_count, st, li);
@@ -568,6 +569,7 @@ cudaError_t launch_search(tp_policy *p, Ctx &c, const Prep &pr, int idx, int cnt
 // polling its flag, so the call makes no memcpy, records no event and never blocks in the driver.
 int run_search_fast(tp_policy *p, Ctx &c, const Prep &pr, TpKey *key, tp_result *info) {
     const unsigned epoch = ++c.epoch ? c.epoch : ++c.epoch; // never 0
+    (void)cudaGetLastError();
     TP_CUDA(p, tp_launch_exhaustive_lex_small(p->d_weight, p->n, p->d_binom, pr.rq, c.d_fast, epoch, c.stream));
     unsigned spins = 0;
     while (c.h_fast->flag != epoch) {
@@ -777,6 +779,15 @@ int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
         return TP_OK;
     }
     if (dev < 0 && cudaGetDevice(&dev) != cudaSuccess) { delete p; return TP_ERR_CUDA; }
+    {
+        int count = 0;
+        if (cudaGetDeviceCount(&count) != cudaSuccess || dev >= count) {
+            (void)cudaGetLastError(); // (leave no stale error behind for the caller's, or our own, next launch check)
+            p->last_cuda_error = "no such CUDA device: " + std::to_string(dev);
+            delete p;
+            return TP_ERR_CUDA;
+        }
+    }
     p->cuda_device = dev;
     int rc = [&]() -> int {
         DeviceGuard guard(dev);
@@ -1074,6 +1085,7 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         if (plan_at)
             TP_CUDA(p, cudaMemcpyAsync(b.d_plans, b.h_plans, plan_at * sizeof(TpPlan), cudaMemcpyHostToDevice, b.stream));
         TP_CUDA(p, cudaMemcpyAsync(b.d_order, b.h_order, n_order * sizeof(TpBatchEntry), cudaMemcpyHostToDevice, b.stream));
+        (void)cudaGetLastError();
         for (size_t g = 0; g < groups.size(); g++) {
             const BatchGroup &grp = groups[g];
             TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + g, (int32_t)n_entries[g], 0};
@@ -1395,6 +1407,7 @@ int tp_allocate_static(const tp_topology *t, const uint8_t *d_weight, const int3
     if (pr.family_only || pr.rq.total > TP_STATIC_MAX_SUBSETS) return TP_ERR_STATIC_SCRATCH;
     cudaStream_t st = (cudaStream_t)cuda_stream;
     TpLaunchInfo li{};
+    (void)cudaGetLastError();
     cudaError_t e = tp_launch_exhaustive_lex_static(d_weight, n, &host.binom[0][0], pr.rq, 0, pr.rq.total,
                                                     (unsigned long long *)d_out, st, &li);
     u64 h_out[3] = {TP_KEY_INF_HI, TP_KEY_INF_HI, 0};
