@@ -690,10 +690,10 @@ static __device__ __noinline__ int tp_tri_family_seed(const TpSmem s, int n_grou
     return best;
 }
 
-// Once per request and block: stage the request, build the tables, seed the bound.  Three
-// barriers: (1) the descriptor's small tables, (2) the weights in canonical order (gathered
-// from global memory straight into the byte table and the 16-bit reversed table), (3) the S3
-// table and the seeds.  g_bound_inv: a global word shared by the grid (single request) through
+// Once per request and block: stage the request, build the tables, seed the bound.  Two
+// barriers: after (1) the descriptor's small tables + (2) the weights in canonical order (gathered
+// from global memory straight into the byte table and the 16-bit reversed table), and after (3)
+// the S3 table and the seeds.  g_bound_inv: a global word shared by the grid (single request) through
 // which blocks exchange the best Family score they know, stored as 0x7FFFFFFF - score so that a
 // zeroed word means "none"; null for a batch request, where the block owns the request.
 template <int M, int DW>
@@ -702,7 +702,6 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
                                           unsigned *g_bound_inv) {
     unsigned char *const smem = tp_split_smem;
     __shared__ uint8_t s_hmap[tp_tri_off(TP_TRI_GC)];
-    __shared__ uint8_t s_canon[TP_MAX_N], s_req[TP_MAX_N];
     const int n = rq->n, k = rq->k, n_req = rq->n_req;
     const int gcap = plan->tri_gcap;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x, nt = blockDim.x;
@@ -742,12 +741,10 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
     }
     if (lane == 0) *(u64 *)(bstack + TP_TRI_WB_COUNT) = 0;
     for (int i = tid; i < n; i += nt) {
-        s_canon[i] = rq->canon[i];
         s.group[i] = rq->group_of[i];
         s.gstart[i] = rq->gstart[i];
         s.gsize[i] = rq->gsize[i];
     }
-    for (int i = tid; i < n_req; i += nt) s_req[i] = rq->req[i];
     for (int a = warp; a <= n; a += TP_TRI_WARPS)
         for (int j = lane; j <= k; j += 32) s.binom[a * (k + 1) + j] = binom_g[a * TP_BINOM_COLS + j];
     for (int i = tid; i < plan->n_entries; i += nt) {
@@ -761,14 +758,14 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         tp_tri_pair_info[g] = make_uint4(16u * tp_tri_pair_base(g), 16u * tp_tri_off(g + 1), 16u * tp_tri_off(g), 0u);
     for (int h = tid; h < gcap; h += nt)
         for (int c = tp_tri_off(h); c < tp_tri_off(h + 1); c++) s_hmap[c] = (uint8_t)h;
-    __syncthreads();
     TP_TRI_STAMP(2);
-    // ---- (2) weights: canonical byte table (seeds) and 16-bit reversed table (everything else) ----
+    // ---- (2) weights: canonical byte table (seeds) and 16-bit reversed table (everything else); the
+    // canonical order is read from the descriptor itself, so that no barrier separates (1) and (2) ----
     for (int r = warp; r < n; r += TP_TRI_WARPS) { // one row per warp pass: no divisions
-        const uint8_t *wrow = W + (int)s_canon[r] * nd;
+        const uint8_t *wrow = W + (int)rq->canon[r] * nd;
         uint16_t *prow = wp + (n - 1 - r) * rsp;
         for (int c = lane; c < rsp; c += 32) { // reversed column n - 1 - c holds canonical column c
-            const unsigned v = (c < n && c != r) ? wrow[s_canon[c]] : 0u;
+            const unsigned v = (c < n && c != r) ? wrow[rq->canon[c]] : 0u;
             if (c < n) {
                 s.w[r * s.stride + c] = (uint8_t)v;
                 prow[n - 1 - c] = (uint16_t)v;
@@ -780,8 +777,8 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
     for (int i = tid; i < TP_MAX_N; i += nt) {
         unsigned u = 0;
         if (i < n) {
-            const uint8_t *wrow = W + (int)s_canon[i] * nd;
-            for (int r = 0; r < n_req; r++) u += wrow[s_req[r]];
+            const uint8_t *wrow = W + (int)rq->canon[i] * nd;
+            for (int r = 0; r < n_req; r++) u += wrow[rq->req[r]];
             s.u[i] = (uint16_t)u;
             t0[n - 1 - i] = (uint16_t)u;
         } else {
@@ -812,11 +809,10 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         if (left == 0) atomicMin(&tp_tri_bound, sco);
     }
     {
-        // A share per block only where the whole seed would cost a block microseconds AND the search is
-        // long enough for the other blocks' shares to arrive early in it; a small search is mostly over
-        // by then, and with a loose bound most of its leaves would go through the slow path.
-        const bool spread = g_bound_inv && ((1u << min(rq->n_groups, 20)) * (unsigned)(rq->n_groups + 1) > 4096u) &&
-                            rq->total > (1ull << 28);
+        // A share per block only where the search is long enough for the other blocks' shares to arrive
+        // early in it (until then the two cheap seeds above bound it); a small search is mostly over by
+        // then, and with a loose bound most of its leaves would go through the slow path.
+        const bool spread = g_bound_inv && rq->total > (1ull << 28);
         const unsigned first = spread ? blockIdx.x * (unsigned)nt + tid : (unsigned)tid;
         const unsigned stride = spread ? gridDim.x * (unsigned)nt : (unsigned)nt;
         const int sco = tp_tri_family_seed(s, rq->n_groups, k, rq->c_req, first, stride);
