@@ -617,8 +617,56 @@ __global__ void __launch_bounds__(256) tp_int_peak_lds_kernel(unsigned *out, uns
     if ((acc0 ^ acc1) == 0x12345678u) out[0] = acc0;
 }
 
+// variants 6..8: can the FMA pipe take part of the packed add-min work?  Per accumulator and iteration four
+// "min(acc, p + w)" steps: 6 = four VIADDMNMX.U16x2 (alu pipe, half rate); 7 = all four as IMAD (p + w * one, fma
+// pipe) + VIMNMX3.U16x2 (two steps per min3); 8 = two VIADDMNMX + (two IMAD + one VIMNMX3): both pipes at once.
+template <int VARIANT>
+__global__ void __launch_bounds__(256) tp_int_peak_mix_kernel(unsigned *out, unsigned seed, int iters, unsigned one) {
+    unsigned acc[8], p[4], w[4];
+#pragma unroll
+    for (int i = 0; i < 8; i++) acc[i] = 0x7FFF7FFFu - i;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        p[i] = (seed * (i + 1) + threadIdx.x) & 0x0FFF0FFFu;
+        w[i] = (seed * (i + 5) + threadIdx.x * 3) & 0x0FFF0FFFu;
+    }
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int a = 0; a < 8; a++) {
+            if (VARIANT == 6) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) acc[a] = __viaddmin_u16x2(p[i], w[i], acc[a]);
+            } else if (VARIANT == 7) {
+                unsigned t0, t1, t2, t3;
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t0) : "r"(w[0]), "r"(one), "r"(p[0]));
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t1) : "r"(w[1]), "r"(one), "r"(p[1]));
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t2) : "r"(w[2]), "r"(one), "r"(p[2]));
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t3) : "r"(w[3]), "r"(one), "r"(p[3]));
+                acc[a] = __vimin3_u16x2(t0, t1, acc[a]);
+                acc[a] = __vimin3_u16x2(t2, t3, acc[a]);
+            } else {
+                unsigned t0, t1;
+                acc[a] = __viaddmin_u16x2(p[0], w[0], acc[a]);
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t0) : "r"(w[2]), "r"(one), "r"(p[2]));
+                acc[a] = __viaddmin_u16x2(p[1], w[1], acc[a]);
+                asm volatile("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t1) : "r"(w[3]), "r"(one), "r"(p[3]));
+                acc[a] = __vimin3_u16x2(t0, t1, acc[a]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 4; i++) w[i] ^= acc[i] & 0x00010001u; // keep the operands loop-variant
+    }
+    unsigned r = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) r ^= acc[i];
+    if (r == 0x12345678u) out[0] = r;
+}
+
 cudaError_t tp_launch_int_peak(int variant, int blocks, int iters, unsigned *d_out, cudaStream_t st) {
     switch (variant) {
+    case 6: tp_int_peak_mix_kernel<6><<<blocks, 256, 0, st>>>(d_out, 12345u, iters / 2, 1u); return cudaGetLastError();
+    case 7: tp_int_peak_mix_kernel<7><<<blocks, 256, 0, st>>>(d_out, 12345u, iters / 2, 1u); return cudaGetLastError();
+    case 8: tp_int_peak_mix_kernel<8><<<blocks, 256, 0, st>>>(d_out, 12345u, iters / 2, 1u); return cudaGetLastError();
     case 0: tp_int_peak_kernel<0><<<blocks, 256, 0, st>>>(d_out, 12345u, iters); break;
     case 1: tp_int_peak_kernel<1><<<blocks, 256, 0, st>>>(d_out, 12345u, iters); break;
     case 2: tp_int_peak_kernel<2><<<blocks, 256, 0, st>>>(d_out, 12345u, iters); break;

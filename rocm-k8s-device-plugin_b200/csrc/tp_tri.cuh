@@ -81,29 +81,50 @@ __device__ __forceinline__ unsigned tp_lds16(unsigned addr) {
     return v;
 }
 
+// Two "acc = min(acc, vt + word)" steps.  With TP_TRI_MIN3 they are IMAD + IMAD + VIMNMX3.U16x2: the adds go to
+// the FMA pipe (a multiply by a register that holds 1 keeps ptxas from turning them back into ALU adds) and the
+// half-rate ALU pipe sees one instruction for two steps instead of two VIADDMNMX.  As a microbenchmark that is
+// 1.77 x the add-min rate (scripts/int_peaks.py, variants 6 / 7: 16.4 T against 29.0 T steps/s); in this kernel
+// it is 12-17 % SLOWER (8 of 64: 0.358 against 0.321 ms, 8 of 80: 1.86 against 1.58 ms): three issue slots
+// for two steps instead of two, and the kernel as a whole is short of issue slots, not of ALU cycles.  Off.
+#ifndef TP_TRI_MIN3
+#define TP_TRI_MIN3 0
+#endif
+__device__ __forceinline__ unsigned tp_step2(unsigned acc, unsigned v0, unsigned w0, unsigned v1, unsigned w1, unsigned one) {
+#if TP_TRI_MIN3
+    unsigned t0, t1;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t0) : "r"(w0), "r"(one), "r"(v0));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t1) : "r"(w1), "r"(one), "r"(v1));
+    return __vimin3_u16x2(t0, t1, acc);
+#else
+    (void)one;
+    return __viaddmin_u16x2(v1, w1, __viaddmin_u16x2(v0, w0, acc));
+#endif
+}
+
 // One row pair of both leaves of a pass.  H is a compile-time constant: every register index and
 // every table offset below is an immediate.  tA, tB: shared addresses of the two leaves' tables.
 template <int H>
 __device__ __forceinline__ void tp_tri_rowpair(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                               unsigned &runA, unsigned &runB) {
+                                               unsigned &runA, unsigned &runB, unsigned one) {
     constexpr int NCH = tp_tri_chunks(H), OFF = tp_tri_off(H);
     unsigned accA = TP_BIG2 + TP_BIG2, accB = TP_BIG2 + TP_BIG2;
 #pragma unroll
     for (int c = 0; c < NCH; c++) {
         const uint4 a = tp_lds128(tA + (OFF + c) * 16), b = tp_lds128(tB + (OFF + c) * 16);
-        accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
-        accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
         if (4 * c + 1 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 1], a.y, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 1], b.y, accB);
-        }
-        if (4 * c + 2 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 2], a.z, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 2], b.z, accB);
+            accA = tp_step2(accA, VT[4 * c + 0], a.x, VT[4 * c + 1], a.y, one);
+            accB = tp_step2(accB, VT[4 * c + 0], b.x, VT[4 * c + 1], b.y, one);
+        } else {
+            accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
+            accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
         }
         if (4 * c + 3 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 3], a.w, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 3], b.w, accB);
+            accA = tp_step2(accA, VT[4 * c + 2], a.z, VT[4 * c + 3], a.w, one);
+            accB = tp_step2(accB, VT[4 * c + 2], b.z, VT[4 * c + 3], b.w, one);
+        } else if (4 * c + 2 <= 2 * H) {
+            accA = __viaddmin_u16x2(VT[4 * c + 2], a.z, accA);
+            accB = __viaddmin_u16x2(VT[4 * c + 2], b.z, accB);
         }
     }
     const unsigned pk = __byte_perm(VT[2 * H], VT[2 * H + 1], 0x5410); // VT[2H] | VT[2H+1] << 16
@@ -130,7 +151,8 @@ __device__ __forceinline__ unsigned tp_pack_lo(unsigned a, unsigned b) { // a.lo
 }
 template <int H>
 __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                                  unsigned &runA, unsigned &runB, uint4 (&bA)[2], uint4 (&bB)[2]) {
+                                                  unsigned &runA, unsigned &runB, uint4 (&bA)[2], uint4 (&bB)[2],
+                                                  unsigned one) {
     constexpr int NCH = tp_tri_chunks(H), OFF = tp_tri_off(H);
     unsigned accA = TP_BIG2 + TP_BIG2, accB = TP_BIG2 + TP_BIG2;
 #pragma unroll
@@ -147,19 +169,19 @@ __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NR
             bB[cur ^ 1] = tp_lds128v(tB + tp_tri_off(H > 0 ? H - 1 : 0) * 16);
         }
         const uint4 a = bA[cur], b = bB[cur];
-        accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
-        accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
         if (4 * c + 1 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 1], a.y, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 1], b.y, accB);
-        }
-        if (4 * c + 2 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 2], a.z, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 2], b.z, accB);
+            accA = tp_step2(accA, VT[4 * c + 0], a.x, VT[4 * c + 1], a.y, one);
+            accB = tp_step2(accB, VT[4 * c + 0], b.x, VT[4 * c + 1], b.y, one);
+        } else {
+            accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
+            accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
         }
         if (4 * c + 3 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 3], a.w, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 3], b.w, accB);
+            accA = tp_step2(accA, VT[4 * c + 2], a.z, VT[4 * c + 3], a.w, one);
+            accB = tp_step2(accB, VT[4 * c + 2], b.z, VT[4 * c + 3], b.w, one);
+        } else if (4 * c + 2 <= 2 * H) {
+            accA = __viaddmin_u16x2(VT[4 * c + 2], a.z, accA);
+            accB = __viaddmin_u16x2(VT[4 * c + 2], b.z, accB);
         }
     }
     const unsigned pk = tp_pack_lo(VT[2 * H], VT[2 * H + 1]); // VT[2H] | VT[2H+1] << 16
@@ -170,12 +192,12 @@ __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NR
 #if TP_TRI_PREFETCH
 #define TP_TRI_CASE(H)                                                                               \
     case H:                                                                                          \
-        tp_tri_rowpair_pf<(H)>(VT, tA, tB, runA, runB, bufA, bufB);                                  \
+        tp_tri_rowpair_pf<(H)>(VT, tA, tB, runA, runB, bufA, bufB, one);                             \
         [[fallthrough]];
 #else
 #define TP_TRI_CASE(H)                                   \
     case H:                                              \
-        tp_tri_rowpair<(H)>(VT, tA, tB, runA, runB);     \
+        tp_tri_rowpair<(H)>(VT, tA, tB, runA, runB, one);     \
         [[fallthrough]];
 #endif
 #define TP_TRI_CASE8(B)                                                                          \
@@ -350,9 +372,9 @@ __device__ __forceinline__ unsigned tp_lds8v(unsigned addr) {
 template <int H>
 struct TpTriRows {
     static __device__ __forceinline__ void run(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                               unsigned &runA, unsigned &runB) {
-        tp_tri_rowpair<H>(VT, tA, tB, runA, runB);
-        if constexpr (H > 0) TpTriRows<H - 1>::run(VT, tA, tB, runA, runB);
+                                               unsigned &runA, unsigned &runB, unsigned one) {
+        tp_tri_rowpair<H>(VT, tA, tB, runA, runB, one);
+        if constexpr (H > 0) TpTriRows<H - 1>::run(VT, tA, tB, runA, runB, one);
     }
 };
 
@@ -377,7 +399,7 @@ struct TpTriRows {
             constexpr unsigned OFFB = (unsigned)tp_tri_pair_base(G) * 16u;                              \
             constexpr unsigned OFFA = OFFB + (unsigned)tp_tri_off((G) + 1) * 16u;                       \
             unsigned runA = TP_BIG2 + TP_BIG2, runB = TP_BIG2 + TP_BIG2;                                \
-            TpTriRows<(G)>::run(VT, tbl + OFFA, tbl + OFFB, runA, runB);                                \
+            TpTriRows<(G)>::run(VT, tbl + OFFA, tbl + OFFB, runA, runB, one);                           \
             xm = __vimin3_u16x2(xm, runA + VT[2 * (G) + 2], runB + VT[2 * (G) + 1]);                    \
             if constexpr ((G) >= TP_TRI_GB || (G) == 0) {                                               \
                 if (__vminu2(xm, room2) != room2) {                                                     \
@@ -406,6 +428,7 @@ __device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned tl, unsigned
     auto vt_at = [&](int j) -> int { // (V + T)[j] of this lane: two 16-bit loads
         return (int)tp_lds16(va + (unsigned)((j >> 3) * 512 + (j & 7) * 2)) + (int)tp_lds16(tl + 2u * (unsigned)j);
     };
+    const unsigned one = (unsigned)(*(volatile int *)&tp_tri_blk.gcap >> 30) + 1u; // 1, but not to the compiler
     const int room = *(volatile int *)&tp_tri_bound - base + 1; // a total below this is a candidate
     // (a lane without a real A never reports: its threshold is 0)
     const unsigned room2 = gcap_active > 0 ? (unsigned)min(max(room, 0), 0xFFFF) * 0x10001u : 0u;
