@@ -39,6 +39,12 @@ while time.time() < t_end:
     pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
     ids = [d.Id for d in devs]
     n_topo += 1
+    if n_topo % 3 == 0:  # forced small work items and cut values: the work plan's second level on every request
+        pol.set_tuning(item_cap=64 + gen.below(400), item_cap1=64 + gen.below(300))
+    spl = None
+    if n_topo % 4 == 0:  # the round-1 kernel beside the default choice: same key
+        spl = tp.BestEffortPolicy(cuda_device=0, kernel=tp.KERNEL_SPLIT)
+        spl.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
     for _ in range(40):
         av, rq, k = topo.random_request(gen, ids, kmax=min(9, len(ids) - 1), p_choices=(0.3, 0.6, 0.9), max_required=3)
         # keep the oracle's BFS (k-permutations on unpartitioned nodes) and the GPU search bounded
@@ -53,5 +59,11 @@ while time.time() < t_end:
             sys.exit(1)
         n_req += 1
         kernels[pol.last["kernel"]] = kernels.get(pol.last["kernel"], 0) + 1
+        if spl is not None and ref.last["searched"]:
+            if spl.Allocate(av, rq, k) != want or spl.last["key"] != pol.last["key"]:
+                print("SPLIT/TRI MISMATCH", dict(av=av, rq=rq, k=k, split=spl.last, default=pol.last))
+                sys.exit(1)
     pol.close()
+    if spl is not None:
+        spl.close()
 print(f"fuzz ok: {n_topo} topologies, {n_req} requests, kernels {kernels}")
