@@ -260,6 +260,13 @@ int tp_descriptor_bytes(int32_t with_plan);
  * TP_SPLIT_CAP1; nothing on the request path reads the environment.  Not thread-safe against running calls. */
 void tp_set_tuning(tp_policy *p, int32_t walk_q, uint64_t item_cap, uint64_t item_cap1);
 
+/* Development hook for tp_allocate_batch (no counterpart in the reference): a request above 2^share_shift
+ * subsets is cut into shares taken by different blocks (default: 24, 26 or 28 by the number of heavy requests in
+ * the batch), a share into about items_per_warp work items per warp (default 4); light_first != 0 swaps the two waves of the batch (the light requests go to the
+ * GPU first).  0 = default.  The first two are also read ONCE, in tp_create, from TP_BATCH_SHARE_SHIFT and
+ * TP_BATCH_ITEMS_PER_WARP.  Not thread-safe against running calls. */
+void tp_set_batch_tuning(tp_policy *p, int32_t share_shift, int32_t items_per_warp, int32_t light_first);
+
 /* Roofline denominator: dependency-free integer-ALU microbenchmark on the given device.
  * variant 0: IADD3 only (alu pipe); 1: IADD3 + IMAD mix (alu + fma pipes); 2: packed
  * 16x2 min (VIMNMX).  *gops receives 10^9 lane-operations per second. */

@@ -138,6 +138,8 @@ def lib() -> C.CDLL:
     L.tp_exchange_destroy.restype = None
     L.tp_set_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_uint64, C.c_uint64]
     L.tp_set_tuning.restype = None
+    L.tp_set_batch_tuning.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+    L.tp_set_batch_tuning.restype = None
     L.tp_allocate_static.argtypes = [C.POINTER(TpTopology), C.c_void_p, I32P, C.c_int32, I32P, C.c_int32,
                                      C.c_int32, C.c_void_p, C.c_void_p, I32P, C.POINTER(TpResult)]
     L.tph_new.restype = C.c_void_p
@@ -242,6 +244,10 @@ class BestEffortPolicy:
     def set_tuning(self, walk_q=0, item_cap=0, item_cap1=0):
         """tp_set_tuning (development hook): override the work plan of requests prepared from now on."""
         lib().tp_set_tuning(self.handle, walk_q, item_cap, item_cap1)
+
+    def set_batch_tuning(self, share_shift=0, items_per_warp=0, light_first=False):
+        """tp_set_batch_tuning (development hook): the work plan of tp_allocate_batch from now on."""
+        lib().tp_set_batch_tuning(self.handle, share_shift, items_per_warp, 1 if light_first else 0)
 
     def GlobalOptimum(self, available, required, size):
         """tp_global_optimum: the best set over ALL subsets (advisory; not what the reference returns)."""

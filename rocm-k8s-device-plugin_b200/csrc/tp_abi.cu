@@ -62,12 +62,24 @@ struct Prep {
     u64 family_masks = 0;     // kernel FAMILY: 2^groups bitmasks to visit
     int shards = 1;           // how many shards the search will be split into (sizes the SPLIT items)
     bool batch = false;       // prepared for tp_allocate_batch: a block, not the grid, takes each share
+    int share_shift = 24;     // ... and a request above 2^share_shift subsets is cut into shares
 };
+
+// fn(t) for t in [0, nthreads): the calling thread takes t == 0
+template <class F>
+void run_threads(int nthreads, F fn) {
+    std::vector<std::thread> pool;
+    for (int t = 1; t < nthreads; t++) pool.emplace_back(fn, t);
+    fn(0);
+    for (std::thread &t : pool) t.join();
+}
 
 inline bool uses_plan(int kernel) { return kernel == TP_KERNEL_SPLIT || kernel == TP_KERNEL_TRI; }
 
 // tp_allocate_batch cuts a heavy SPLIT / TRI request into this many shares, each taken by one block.
-inline int batch_shares(u64 total) { return total <= (1ull << 24) ? 1 : (int)std::min<u64>(16, (total >> 24) + 1); }
+inline int batch_shares(int shift, u64 total) {
+    return total <= (1ull << shift) ? 1 : (int)std::min<u64>(16, (total >> shift) + 1);
+}
 
 } // namespace
 
@@ -125,7 +137,8 @@ struct tp_policy {
     int kernel = 0;
     u64 exhaustive_limit = 0;
     // development knobs, read from the environment ONCE in tp_create (never on the request path):
-    // TP_SPLIT_Q (walk split), TP_SPLIT_CAP / TP_SPLIT_CAP1 (item sizes), TP_BATCH_TRACE (phase timings)
+    // TP_SPLIT_Q (walk split), TP_SPLIT_CAP / TP_SPLIT_CAP1 (item sizes), TP_BATCH_TRACE (phase timings),
+    // TP_BATCH_SHARE_SHIFT / TP_BATCH_ITEMS_PER_WARP (batch work plan)
     int tune_q = 0;
     u64 tune_cap = 0, tune_cap1 = 0;
     bool batch_trace = false;
@@ -137,17 +150,30 @@ struct tp_policy {
     std::mutex mu;
     std::condition_variable cv;
     std::string last_cuda_error;
-    // tp_allocate_batch: one batch at a time per policy; buffers grow on demand
+    // tp_allocate_batch: kBatchSlots batches in flight per policy, each with buffers (grown on demand), a copy
+    // stream and kBatchSide kernel streams of its own
+    static constexpr int kBatchSlots = 2, kBatchSide = 4;
     struct Batch {
-        std::mutex mu;
-        cudaStream_t stream = nullptr;
+        cudaStream_t stream = nullptr;          // H2D of the waves, D2H of the results
+        cudaStream_t side[kBatchSide] = {};     // the kernel groups, round robin
+        cudaEvent_t ev_in[2] = {}, ev_done[kBatchSide] = {};
         size_t cap_reqs = 0, cap_plans = 0;
         TpReq *h_reqs = nullptr, *d_reqs = nullptr;
         TpPlan *h_plans = nullptr, *d_plans = nullptr;
         TpBatchEntry *h_order = nullptr, *d_order = nullptr;
         TpBatchOut *h_results = nullptr, *d_results = nullptr;
         unsigned *d_grab = nullptr; // one counter per kernel group
-    } batch;
+    } batches[kBatchSlots];
+    std::mutex batch_mu;
+    std::condition_variable batch_cv;
+    std::vector<int> free_batches{1, 0};
+    // batch work plan: a request above 2^shift subsets is cut into (total >> shift) + 1 shares (at most 16), each
+    // taken by one block (0: by the number of heavy requests in the batch -- many of them balance the SMs without
+    // being cut, and every share pays the block's table build again); a share is cut into about
+    // batch_items_per_warp items per warp
+    int batch_share_shift = 0;
+    int batch_items_per_warp = 4;
+    bool batch_light_first = false; // wave order (tuning aid): the light requests first
 };
 
 namespace {
@@ -232,6 +258,12 @@ void batch_release(tp_policy::Batch &b) {
     if (b.d_results) cudaFree(b.d_results);
     if (b.d_grab) cudaFree(b.d_grab);
     if (b.stream) cudaStreamDestroy(b.stream);
+    for (cudaStream_t st : b.side)
+        if (st) cudaStreamDestroy(st);
+    for (cudaEvent_t ev : b.ev_in)
+        if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : b.ev_done)
+        if (ev) cudaEventDestroy(ev);
 }
 
 void free_ctx(Ctx &c) {
@@ -290,10 +322,11 @@ bool build_plan(const tp_policy *p, Prep &out) {
     // small (measured sweep on C4: 3.12 ms at 1K, 2.86 ms at 64K; at 8 shards 64K items leave a
     // 0.17 ms tail on a 0.37 ms shard).
     u64 cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (400000ull * (u64)std::max(out.shards, 1))), 65536);
-    // In a batch the eight warps of one block share a share: a handful of items per warp balances
-    // them, and larger items spend less on the per-item set-up (unrank, lane vectors).
+    // In a batch the warps of one block (8 for SPLIT, 16 for TRI) share a share: a handful of items per warp
+    // balances them, and larger items spend less on the per-item set-up (unrank, lane vectors).
+    const u64 batch_lanes = (u64)batch_shares(out.share_shift, rq.total) * 32u * (tri_gcap > 0 ? 16u : (u64)TP_SPLIT_WARPS);
     if (out.batch)
-        cap0 = std::min<u64>(std::max<u64>(2048, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 6)), 65536);
+        cap0 = std::min<u64>(std::max<u64>(2048, rq.total / (batch_lanes * (u64)p->batch_items_per_warp)), 65536);
     // Kernel TRI pays more per item (it builds its lane registers per walked prefix, and an item that
     // covers only part of a prefix runs the generic pass), so its items are larger: the longest one
     // (the heaviest run first) about 45 % of what a warp has to do in the whole search.  Measured on 8 of 64:
@@ -309,7 +342,7 @@ bool build_plan(const tp_policy *p, Prep &out) {
     if (q > 3) {
         const u64 lanes = (u64)p->sm_count * 2 * TP_SPLIT_THREADS;
         u64 cap1 = std::max<u64>(cap0, rq.total / (lanes * (u64)std::max(out.shards, 1) * 4));
-        if (out.batch) cap1 = std::max<u64>(cap0, rq.total / ((u64)batch_shares(rq.total) * TP_SPLIT_THREADS * 4));
+        if (out.batch) cap1 = std::max<u64>(cap0, rq.total / (batch_lanes * 4));
         if (p->tune_cap1) cap1 = std::max<u64>(64, p->tune_cap1); // tuning aid
         int bs = q - 1;
         while (bs < n && p->binom[bs][q - 1] <= cap1) bs++;
@@ -771,6 +804,8 @@ int tp_create(const tp_topology *t, const tp_options *o, tp_policy **out) {
     if (const char *env = getenv("TP_SPLIT_CAP")) p->tune_cap = strtoull(env, nullptr, 10);
     if (const char *env = getenv("TP_SPLIT_CAP1")) p->tune_cap1 = strtoull(env, nullptr, 10);
     p->batch_trace = getenv("TP_BATCH_TRACE") != nullptr;
+    if (const char *env = getenv("TP_BATCH_SHARE_SHIFT")) p->batch_share_shift = std::max(20, std::min(40, atoi(env)));
+    if (const char *env = getenv("TP_BATCH_ITEMS_PER_WARP")) p->batch_items_per_warp = std::max(1, atoi(env));
     int dev = o ? o->cuda_device : -1;
     if (dev == TP_DEVICE_NONE) { // host-only handle: validation, sharding arithmetic and tp_decode work,
         p->host_only = true;     // every entry point that would search returns TP_ERR_CUDA
@@ -845,7 +880,7 @@ void tp_destroy(tp_policy *p) {
     {
         DeviceGuard guard(p->cuda_device);
         for (Ctx &c : p->ctxs) free_ctx(c);
-        batch_release(p->batch);
+        for (tp_policy::Batch &b : p->batches) batch_release(b);
         if (p->d_weight) cudaFree(p->d_weight);
         if (p->d_binom) cudaFree(p->d_binom);
     }
@@ -904,11 +939,32 @@ namespace {
 
 constexpr int kBatchMaxGroups = 64;
 
-int batch_reserve(tp_policy *p, size_t n_reqs, size_t n_plans) {
-    tp_policy::Batch &b = p->batch;
+struct BatchLease { // one of the policy's batch slots, for the length of a tp_allocate_batch call
+    tp_policy *p;
+    int idx;
+    explicit BatchLease(tp_policy *pol) : p(pol) {
+        std::unique_lock<std::mutex> lk(p->batch_mu);
+        p->batch_cv.wait(lk, [&] { return !p->free_batches.empty(); });
+        idx = p->free_batches.back();
+        p->free_batches.pop_back();
+    }
+    ~BatchLease() {
+        {
+            std::lock_guard<std::mutex> lk(p->batch_mu);
+            p->free_batches.push_back(idx);
+        }
+        p->batch_cv.notify_one();
+    }
+    tp_policy::Batch &slot() { return p->batches[idx]; }
+};
+
+int batch_reserve(tp_policy *p, tp_policy::Batch &b, size_t n_reqs, size_t n_plans) {
     if (!b.stream) {
         TP_CUDA(p, cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
-        TP_CUDA(p, cudaMalloc((void **)&b.d_grab, kBatchMaxGroups * sizeof(unsigned)));
+        for (cudaStream_t &st : b.side) TP_CUDA(p, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        for (cudaEvent_t &ev : b.ev_in) TP_CUDA(p, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        for (cudaEvent_t &ev : b.ev_done) TP_CUDA(p, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+        TP_CUDA(p, cudaMalloc((void **)&b.d_grab, 2 * kBatchMaxGroups * sizeof(unsigned)));
     }
     if (n_reqs > b.cap_reqs) {
         const size_t cap = std::max<size_t>(n_reqs, 256) * 5 / 4;
@@ -945,16 +1001,36 @@ int batch_reserve(tp_policy *p, size_t n_reqs, size_t n_plans) {
 struct BatchGroup {
     int kernel, a, b, c; // LEX: (k', -, -); SPLIT / TRI: (p, q, lane-vector class)
     int max_n = 0, max_k = 0, max_gcap = 0;
+    u64 work = 0;             // subsets of its members
     std::vector<int> members; // request indices
 };
 
 } // namespace
 
-// All requests of one RPC in a handful of launches: requests are prepared on the host (in
-// parallel), grouped by the kernel instantiation they need, and each group runs as ONE persistent
-// launch in which a block owns a whole request (heaviest first).  Requests the reference answers
-// without searching never reach the GPU; the rare ones outside the batch kernels (Family-only)
-// go through tp_allocate.
+// (a failed call may leave earlier launches of this batch in flight: wait for them before the slot is handed back)
+#define TP_BATCH_CUDA(call)                                                                   \
+    do {                                                                                      \
+        cudaError_t e__ = (call);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            {                                                                                 \
+                std::lock_guard<std::mutex> lk__(p->mu);                                      \
+                p->last_cuda_error = std::string(#call) + ": " + cudaGetErrorString(e__);     \
+            }                                                                                 \
+            for (cudaStream_t st__ : b.side) cudaStreamSynchronize(st__);                     \
+            cudaStreamSynchronize(b.stream);                                                  \
+            (void)cudaGetLastError();                                                         \
+            return TP_ERR_CUDA;                                                               \
+        }                                                                                     \
+    } while (0)
+
+// All requests of one RPC in a handful of launches.  Requests are prepared on the host (in parallel),
+// grouped by the kernel instantiation they need, and each group runs as ONE persistent launch in which
+// a block owns a whole request, or one share of a heavy one (heaviest first).  The batch goes in two
+// WAVES: the requests that search longest (k' >= 6) are prepared, staged and launched first, and the
+// host prepares the rest while the GPU works on them; groups run on a few streams, so that the light
+// groups fill the SMs the heavy group's last blocks leave.  Requests the reference answers without
+// searching never reach the GPU; the rare ones outside the batch kernels (Family-only) go through
+// tp_allocate.  Up to kBatchSlots calls run concurrently on one policy, each on buffers of its own.
 int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, int32_t *out, int32_t out_stride,
                       int32_t *status, tp_result *infos) {
     if (!p || n_requests < 0 || (n_requests && (!rqs || !out || !status))) return TP_ERR_BAD_ARGUMENT;
@@ -972,172 +1048,220 @@ int tp_allocate_batch(tp_policy *p, int32_t n_requests, const tp_request *rqs, i
         return std::chrono::duration<double, std::milli>(now() - t0).count();
     };
     const auto t_start = now();
-    std::vector<Prep> preps(n_requests);
-    {
-        const unsigned hw = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
-        const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_requests / 64 + 1));
-        auto work = [&](int t) {
-            for (int i = t; i < n_requests; i += nthreads)
-                prepare(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required, rqs[i].size,
-                        preps[i], 1, true);
-        };
-        std::vector<std::thread> pool;
-        for (int t = 1; t < nthreads; t++) pool.emplace_back(work, t);
-        work(0);
-        for (std::thread &t : pool) t.join();
+    // ---- which wave, and upper bounds on what the batch needs (before anything is prepared) ----
+    std::vector<int> wave[2];
+    size_t out_bound = 0, plan_bound = 0;
+    int share_shift = p->batch_share_shift;
+    if (share_shift == 0) {
+        int n_heavy = 0;
+        for (int i = 0; i < n_requests; i++) n_heavy += rqs[i].size - rqs[i].n_required >= 6;
+        share_shift = n_heavy >= 4 * p->sm_count ? 28 : n_heavy >= p->sm_count ? 26 : 24;
     }
-    const double t_prepare = ms_since(t_start);
-    std::vector<BatchGroup> groups;
-    std::vector<int> singles; // served by tp_allocate after the batch
-    size_t n_plans = 0;
     for (int i = 0; i < n_requests; i++) {
-        const Prep &pr = preps[i];
-        if (infos) memset(&infos[i], 0, sizeof(tp_result));
-        if (rqs[i].size > out_stride && !pr.status) { status[i] = TP_ERR_BAD_ARGUMENT; continue; }
-        if (pr.status) { status[i] = pr.status; continue; }
-        if (pr.shortcut) {
-            memcpy(out + (size_t)i * out_stride, pr.shortcut == 1 ? rqs[i].available : rqs[i].required,
-                   sizeof(int32_t) * rqs[i].size);
-            status[i] = rqs[i].size;
-            continue;
-        }
-        if (pr.family_only || pr.kernel == TP_KERNEL_FAMILY) { singles.push_back(i); continue; }
-        // a LEX request gets ONE block in a batch group; a large one (scores beyond the packed kernels' 16-bit
-        // range can hold up to 2^38 subsets) would keep that block, and the whole RPC, busy for minutes
-        if (pr.kernel == TP_KERNEL_LEX && pr.rq.total > (1ull << 24)) { singles.push_back(i); continue; }
-        BatchGroup key;
-        key.kernel = pr.kernel;
-        if (uses_plan(pr.kernel)) {
-            const int need = pr.rq.n - pr.plan.p;
-            key.a = pr.plan.p; key.b = pr.plan.q; key.c = need <= 64 ? 64 : need <= 80 ? 80 : need <= 96 ? 96 : 128;
-            n_plans++;
+        const tp_request &r = rqs[i];
+        const int k1 = r.size - r.n_required, n1 = r.n_available - r.n_required;
+        const bool heavy = k1 >= 6 && n1 > k1;
+        wave[(heavy ? 0 : 1) ^ (p->batch_light_first ? 1 : 0)].push_back(i);
+        if (k1 >= 4 && n1 > k1) {
+            plan_bound++;
+            out_bound += (n1 <= TP_MAX_N && k1 < TP_BINOM_COLS) ? (size_t)batch_shares(share_shift, p->binom[n1][k1]) : 16;
         } else {
-            key.a = pr.rq.k; key.b = 0; key.c = 0;
+            out_bound++;
         }
-        size_t g = 0;
-        for (; g < groups.size(); g++)
-            if (groups[g].kernel == key.kernel && groups[g].a == key.a && groups[g].b == key.b && groups[g].c == key.c) break;
-        if (g == groups.size()) {
-            if ((int)groups.size() == kBatchMaxGroups) { singles.push_back(i); if (uses_plan(pr.kernel)) n_plans--; continue; }
-            groups.push_back(key);
-        }
-        groups[g].members.push_back(i);
-        groups[g].max_n = std::max(groups[g].max_n, pr.rq.n);
-        groups[g].max_k = std::max(groups[g].max_k, pr.rq.k);
-        if (pr.kernel == TP_KERNEL_TRI) groups[g].max_gcap = std::max(groups[g].max_gcap, (int)pr.plan.tri_gcap);
     }
+    if (wave[0].empty()) wave[0].swap(wave[1]);
+    std::vector<Prep> preps(n_requests);
+    std::vector<int> singles;       // served by tp_allocate after the batch
+    std::vector<int> searched;      // requests in a batch group, both waves
+    std::vector<int> out_base(n_requests, -1), n_shares(n_requests, 1);
+    std::vector<BatchGroup> groups; // of the wave at hand
     int launches = 0;
-    if (!groups.empty()) {
-        std::lock_guard<std::mutex> batch_lock(p->batch.mu);
-        DeviceGuard guard(p->cuda_device);
+    size_t n_slots = 0, n_plans = 0, n_order = 0, n_out = 0, n_grab = 0;
+    unsigned side_used = 0, side_next = 0;
+    double t_prepare[2] = {0, 0}, t_stage[2] = {0, 0};
+    BatchLease lease(p);
+    tp_policy::Batch &b = lease.slot();
+    DeviceGuard guard(p->cuda_device);
+    for (int w = 0; w < 2; w++) {
+        const std::vector<int> &idx = wave[w];
+        if (idx.empty()) continue;
+        const auto t_wave = now();
+        const int n_w = (int)idx.size();
+        {
+            const unsigned hw = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+            const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_w / 64 + 1));
+            run_threads(nthreads, [&](int t) {
+                for (int j = t; j < n_w; j += nthreads) {
+                    const tp_request &r = rqs[idx[j]];
+                    preps[idx[j]].share_shift = share_shift;
+                    prepare(p, r.available, r.n_available, r.required, r.n_required, r.size, preps[idx[j]], 1, true);
+                }
+            });
+        }
+        t_prepare[w] = ms_since(t_wave);
+        groups.clear();
+        for (int i : idx) {
+            const Prep &pr = preps[i];
+            if (infos) memset(&infos[i], 0, sizeof(tp_result));
+            if (rqs[i].size > out_stride && !pr.status) { status[i] = TP_ERR_BAD_ARGUMENT; continue; }
+            if (pr.status) { status[i] = pr.status; continue; }
+            if (pr.shortcut) {
+                memcpy(out + (size_t)i * out_stride, pr.shortcut == 1 ? rqs[i].available : rqs[i].required,
+                       sizeof(int32_t) * rqs[i].size);
+                status[i] = rqs[i].size;
+                continue;
+            }
+            if (pr.family_only || pr.kernel == TP_KERNEL_FAMILY) { singles.push_back(i); continue; }
+            // a LEX request gets ONE block in a batch group; a large one (scores beyond the packed kernels'
+            // 16-bit range can hold up to 2^38 subsets) would keep that block, and the whole RPC, busy for minutes
+            if (pr.kernel == TP_KERNEL_LEX && pr.rq.total > (1ull << 24)) { singles.push_back(i); continue; }
+            BatchGroup key;
+            key.kernel = pr.kernel;
+            if (uses_plan(pr.kernel)) {
+                const int need = pr.rq.n - pr.plan.p;
+                key.a = pr.plan.p; key.b = pr.plan.q; key.c = need <= 64 ? 64 : need <= 80 ? 80 : need <= 96 ? 96 : 128;
+            } else {
+                key.a = pr.rq.k; key.b = 0; key.c = 0;
+            }
+            size_t g = 0;
+            for (; g < groups.size(); g++)
+                if (groups[g].kernel == key.kernel && groups[g].a == key.a && groups[g].b == key.b && groups[g].c == key.c) break;
+            if (g == groups.size()) {
+                if ((int)groups.size() == kBatchMaxGroups) { singles.push_back(i); continue; }
+                groups.push_back(key);
+            }
+            groups[g].members.push_back(i);
+            groups[g].work += pr.rq.total;
+            groups[g].max_n = std::max(groups[g].max_n, pr.rq.n);
+            groups[g].max_k = std::max(groups[g].max_k, pr.rq.k);
+            if (pr.kernel == TP_KERNEL_TRI) groups[g].max_gcap = std::max(groups[g].max_gcap, (int)pr.plan.tri_gcap);
+        }
+        if (groups.empty()) continue;
+        if (!b.stream || out_bound > b.cap_reqs || (size_t)n_requests > b.cap_reqs || plan_bound > b.cap_plans) {
+            // (only ever before the first launch of this call: the bounds cover both waves)
+            int rc = batch_reserve(p, b, std::max<size_t>((size_t)n_requests, out_bound), plan_bound);
+            if (rc) return rc;
+        }
+        std::sort(groups.begin(), groups.end(), [](const BatchGroup &x, const BatchGroup &y) { return x.work > y.work; });
         // Heavy requests are cut into shares taken by different blocks (the same item striding as
         // multi-GPU shards), so that one big search does not become the tail of its group.
-        auto shares_of = [&](int i) -> int {
-            return uses_plan(preps[i].kernel) ? batch_shares(preps[i].rq.total) : 1;
-        };
-        size_t n_out = 0;
-        std::vector<int> out_base(n_requests, -1);
-        for (const BatchGroup &grp : groups)
-            for (int i : grp.members) {
-                out_base[i] = (int)n_out;
-                n_out += (size_t)shares_of(i);
-            }
-        int rc = batch_reserve(p, std::max<size_t>((size_t)n_requests, n_out), n_plans);
-        if (rc) return rc;
-        tp_policy::Batch &b = p->batch;
-        size_t n_order = 0, plan_at = 0;
+        const size_t slot0 = n_slots, plan0 = n_plans, order0 = n_order;
         std::vector<size_t> first(groups.size()), n_entries(groups.size());
-        std::vector<int> plan_slot(n_requests, -1); // where a request's plan goes in the pinned array
+        std::vector<std::pair<int, int>> placed; // (request, slot) of this wave
         for (size_t g = 0; g < groups.size(); g++) {
             BatchGroup &grp = groups[g];
             std::sort(grp.members.begin(), grp.members.end(),
                       [&](int x, int y) { return preps[x].rq.total > preps[y].rq.total; }); // heaviest first
             first[g] = n_order;
             for (int i : grp.members) {
+                const int S = uses_plan(grp.kernel) ? batch_shares(share_shift, preps[i].rq.total) : 1;
+                if (n_out + (size_t)S > b.cap_reqs || n_order + (size_t)S > b.cap_reqs ||
+                    (uses_plan(grp.kernel) && n_plans >= b.cap_plans)) { // (the bounds above make this unreachable)
+                    singles.push_back(i);
+                    continue;
+                }
+                const int slot = (int)n_slots++;
                 int plan_idx = 0;
                 if (uses_plan(grp.kernel)) {
-                    plan_slot[i] = (int)plan_at;
-                    plan_idx = (int)plan_at++;
+                    plan_idx = (int)n_plans++;
+                    b.h_plans[plan_idx] = preps[i].plan;
                 }
-                const int S = shares_of(i);
+                placed.emplace_back(i, slot);
+                out_base[i] = (int)n_out;
+                n_shares[i] = S;
                 for (int sidx = 0; sidx < S; sidx++)
-                    b.h_order[n_order++] = TpBatchEntry{i, plan_idx, out_base[i] + sidx, (int16_t)sidx, (int16_t)S};
+                    b.h_order[n_order++] = TpBatchEntry{slot, plan_idx, (int)n_out + sidx, (int16_t)sidx, (int16_t)S};
+                n_out += (size_t)S;
+                searched.push_back(i);
             }
             n_entries[g] = n_order - first[g];
         }
-        { // descriptors and plans into the pinned arrays (~2.5 KB per request): worth a few threads
+        { // descriptors into the pinned array (~2 KB per request): worth a few threads
             const unsigned hw = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
-            const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_requests / 512 + 1));
-            auto work = [&](int t) {
-                for (int i = t; i < n_requests; i += nthreads) {
-                    if (out_base[i] < 0) continue; // not in a batch group
-                    b.h_reqs[i] = preps[i].rq;
-                    if (plan_slot[i] >= 0) b.h_plans[plan_slot[i]] = preps[i].plan;
-                }
-            };
-            std::vector<std::thread> pool;
-            for (int t = 1; t < nthreads; t++) pool.emplace_back(work, t);
-            work(0);
-            for (std::thread &t : pool) t.join();
+            const int n_p = (int)placed.size();
+            const int nthreads = (int)std::min<unsigned>(hw, (unsigned)(n_p / 512 + 1));
+            run_threads(nthreads, [&](int t) {
+                for (int j = t; j < n_p; j += nthreads) b.h_reqs[placed[j].second] = preps[placed[j].first].rq;
+            });
         }
-        const double t_stage = ms_since(t_start);
-        TP_CUDA(p, cudaMemcpyAsync(b.d_reqs, b.h_reqs, (size_t)n_requests * sizeof(TpReq), cudaMemcpyHostToDevice, b.stream));
-        if (plan_at)
-            TP_CUDA(p, cudaMemcpyAsync(b.d_plans, b.h_plans, plan_at * sizeof(TpPlan), cudaMemcpyHostToDevice, b.stream));
-        TP_CUDA(p, cudaMemcpyAsync(b.d_order, b.h_order, n_order * sizeof(TpBatchEntry), cudaMemcpyHostToDevice, b.stream));
+        t_stage[w] = ms_since(t_wave) - t_prepare[w];
+        TP_BATCH_CUDA(cudaMemcpyAsync(b.d_reqs + slot0, b.h_reqs + slot0, (n_slots - slot0) * sizeof(TpReq),
+                                      cudaMemcpyHostToDevice, b.stream));
+        if (n_plans > plan0)
+            TP_BATCH_CUDA(cudaMemcpyAsync(b.d_plans + plan0, b.h_plans + plan0, (n_plans - plan0) * sizeof(TpPlan),
+                                          cudaMemcpyHostToDevice, b.stream));
+        TP_BATCH_CUDA(cudaMemcpyAsync(b.d_order + order0, b.h_order + order0, (n_order - order0) * sizeof(TpBatchEntry),
+                                      cudaMemcpyHostToDevice, b.stream));
+        TP_BATCH_CUDA(cudaEventRecord(b.ev_in[w], b.stream));
         (void)cudaGetLastError();
         for (size_t g = 0; g < groups.size(); g++) {
             const BatchGroup &grp = groups[g];
-            TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + g, (int32_t)n_entries[g], 0};
+            if (n_entries[g] == 0) continue;
+            const unsigned sidx = side_next++ % tp_policy::kBatchSide;
+            cudaStream_t st = b.side[sidx];
+            TP_BATCH_CUDA(cudaStreamWaitEvent(st, b.ev_in[w], 0));
+            side_used |= 1u << sidx;
+            TpBatch tb{b.d_order + first[g], b.d_results, b.d_grab + n_grab++, (int32_t)n_entries[g], 0};
             TpLaunchInfo li{};
             if (grp.kernel == TP_KERNEL_TRI)
-                TP_CUDA(p, tp_launch_batch_tri(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
-                                               grp.max_n, grp.max_k, grp.max_gcap, tb, p->sm_count, b.stream, &li));
+                TP_BATCH_CUDA(tp_launch_batch_tri(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
+                                                  grp.max_n, grp.max_k, grp.max_gcap, tb, p->sm_count, st, &li));
             else if (grp.kernel == TP_KERNEL_SPLIT)
-                TP_CUDA(p, tp_launch_batch_split(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
-                                                 grp.max_n, grp.max_k, tb, p->sm_count, b.stream, &li));
+                TP_BATCH_CUDA(tp_launch_batch_split(p->d_weight, p->n, p->d_binom, b.d_reqs, b.d_plans, grp.a, grp.b,
+                                                    grp.max_n, grp.max_k, tb, p->sm_count, st, &li));
             else
-                TP_CUDA(p, tp_launch_batch_lex(p->d_weight, p->n, p->d_binom, b.d_reqs, grp.a, grp.max_n, tb,
-                                               p->sm_count, b.stream, &li));
+                TP_BATCH_CUDA(tp_launch_batch_lex(p->d_weight, p->n, p->d_binom, b.d_reqs, grp.a, grp.max_n, tb,
+                                                  p->sm_count, st, &li));
             launches += li.launches;
         }
-        TP_CUDA(p, cudaMemcpyAsync(b.h_results, b.d_results, n_out * sizeof(TpBatchOut), cudaMemcpyDeviceToHost,
-                                   b.stream));
-        TP_CUDA(p, cudaStreamSynchronize(b.stream));
-        if (trace)
-            fprintf(stderr, "tp_allocate_batch: %d requests, %zu groups: prepare %.2f ms, stage %.2f ms, gpu %.2f ms\n",
-                    n_requests, groups.size(), t_prepare, t_stage - t_prepare, ms_since(t_start) - t_stage);
-        for (const BatchGroup &grp : groups)
-            for (int i : grp.members) {
-                TpKey key = b.h_results[out_base[i]].key; // min over the request's shares
-                u64 scored = b.h_results[out_base[i]].scored;
-                for (int sidx = 1; sidx < shares_of(i); sidx++) {
-                    const TpBatchOut &part = b.h_results[out_base[i] + sidx];
-                    if (tp_key_less(part.key, key)) key = part.key;
-                    scored += part.scored;
-                }
-                status[i] = decode(preps[i], key, rqs[i].required, out + (size_t)i * out_stride);
-                if (infos) {
-                    tp_result &r = infos[i];
-                    r.searched = 1;
-                    r.kernel = preps[i].kernel;
-                    r.subsets_scored = scored;
-                    r.subsets_total = preps[i].rq.total;
-                    r.gpu_launches = launches; // launches of the whole batch (shared by its requests)
-                    r.key.hi = key.hi;
-                    r.key.lo = key.lo;
-                    if (key.hi != TP_KEY_INF_HI) {
-                        r.score = tp_key_score(key);
-                        r.groups_touched = tp_key_groups(key);
-                    }
-                }
+    }
+    const double t_host = ms_since(t_start);
+    if (!searched.empty()) {
+        for (int sidx = 0; sidx < tp_policy::kBatchSide; sidx++)
+            if (side_used >> sidx & 1u) {
+                TP_BATCH_CUDA(cudaEventRecord(b.ev_done[sidx], b.side[sidx]));
+                TP_BATCH_CUDA(cudaStreamWaitEvent(b.stream, b.ev_done[sidx], 0));
             }
+        TP_BATCH_CUDA(cudaMemcpyAsync(b.h_results, b.d_results, n_out * sizeof(TpBatchOut), cudaMemcpyDeviceToHost,
+                                      b.stream));
+        TP_BATCH_CUDA(cudaStreamSynchronize(b.stream));
+    }
+    if (trace)
+        fprintf(stderr,
+                "tp_allocate_batch: %d requests, %d launches: wave 0 (%zu) prepare %.2f stage %.2f ms, wave 1 (%zu) "
+                "prepare %.2f stage %.2f ms, host done at %.2f ms, GPU done at %.2f ms\n",
+                n_requests, launches, wave[0].size(), t_prepare[0], t_stage[0], wave[1].size(), t_prepare[1],
+                t_stage[1], t_host, ms_since(t_start));
+    for (int i : searched) {
+        TpKey key = b.h_results[out_base[i]].key; // min over the request's shares
+        u64 scored = b.h_results[out_base[i]].scored;
+        for (int sidx = 1; sidx < n_shares[i]; sidx++) {
+            const TpBatchOut &part = b.h_results[out_base[i] + sidx];
+            if (tp_key_less(part.key, key)) key = part.key;
+            scored += part.scored;
+        }
+        status[i] = decode(preps[i], key, rqs[i].required, out + (size_t)i * out_stride);
+        if (infos) {
+            tp_result &r = infos[i];
+            r.searched = 1;
+            r.kernel = preps[i].kernel;
+            r.subsets_scored = scored;
+            r.subsets_total = preps[i].rq.total;
+            r.gpu_launches = launches; // launches of the whole batch (shared by its requests)
+            r.key.hi = key.hi;
+            r.key.lo = key.lo;
+            if (key.hi != TP_KEY_INF_HI) {
+                r.score = tp_key_score(key);
+                r.groups_touched = tp_key_groups(key);
+            }
+        }
     }
     for (int i : singles)
         status[i] = tp_allocate(p, rqs[i].available, rqs[i].n_available, rqs[i].required, rqs[i].n_required,
                                 rqs[i].size, out + (size_t)i * out_stride, infos ? infos + i : nullptr);
     return TP_OK;
 }
+#undef TP_BATCH_CUDA
 
 int tp_search_resident(tp_policy *p, const int32_t *avail, int32_t n_avail, const int32_t *req, int32_t n_req,
                        int32_t size, int32_t shard_index, int32_t shard_count, int32_t iters, float *ms,
@@ -1432,6 +1556,13 @@ int tp_allocate_static(const tp_topology *t, const uint8_t *d_weight, const int3
 }
 
 int tp_descriptor_bytes(int32_t with_plan) { return (int)(sizeof(TpReq) + (with_plan ? sizeof(TpPlan) : 0)); }
+
+void tp_set_batch_tuning(tp_policy *p, int32_t share_shift, int32_t items_per_warp, int32_t light_first) {
+    if (!p) return;
+    p->batch_share_shift = share_shift > 0 ? std::max(20, std::min(40, (int)share_shift)) : 0;
+    p->batch_items_per_warp = items_per_warp > 0 ? items_per_warp : 4;
+    p->batch_light_first = light_first != 0;
+}
 
 void tp_set_tuning(tp_policy *p, int32_t walk_q, uint64_t item_cap, uint64_t item_cap1) {
     if (!p) return;

@@ -1,5 +1,5 @@
-"""Pod storm (BASELINE C5) against the item-size knob: python scripts/storm_sweep.py"""
-import os, sys, time
+"""Pod storm (BASELINE C5) against the batch work-plan knobs: python scripts/storm_sweep.py"""
+import os, sys, time, threading
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
 import topo
@@ -19,10 +19,32 @@ while len(reqs) < 10000:
 pol = tp.BestEffortPolicy(cuda_device=0)
 pol.InitWithWeights([tp.Device(d.Id, d.NodeId, d.NumaNode, d.DevId) for d in devs], pairs)
 batch = tp.Batch(pol, reqs)
-for cap in (0, 2048, 4096, 8192, 16384, 32768, 65536):
-    pol.set_tuning(item_cap=cap)
+batch.run()
+want, _ = batch.results()
+
+
+def timed(label):
     batch.run()
     ts = []
     for _ in range(3):
         t = time.perf_counter(); batch.run(); ts.append(time.perf_counter() - t)
-    print("cap %d: batch %.2f ms" % (cap, min(ts) * 1e3), flush=True)
+    got, _ = batch.results()
+    print("%s: batch %.2f ms%s" % (label, min(ts) * 1e3, "" if got == want else "  MISMATCH"), flush=True)
+
+
+for shift in (24, 25, 26, 27, 28):
+    for ipw in (4, 8, 16):
+        pol.set_batch_tuning(share_shift=shift, items_per_warp=ipw)
+        timed("shift %d items/warp %d" % (shift, ipw))
+pol.set_batch_tuning(light_first=True)
+timed("defaults, light wave first")
+pol.set_batch_tuning()
+timed("defaults")
+# two batches at once on one policy (separate buffers and streams per call)
+b2 = tp.Batch(pol, reqs)
+b2.run()
+t = time.perf_counter()
+th = threading.Thread(target=b2.run)
+th.start(); batch.run(); th.join()
+dt = time.perf_counter() - t
+print("two concurrent batches: %.2f ms for both%s" % (dt * 1e3, "" if b2.results()[0] == want and batch.results()[0] == want else "  MISMATCH"))

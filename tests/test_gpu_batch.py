@@ -58,6 +58,36 @@ def test_pod_storm_batch_matches_reference():
     pol.close()
 
 
+def test_two_batches_at_once_and_share_cuts():
+    """Two tp_allocate_batch calls on one policy at the same time (separate buffers and streams per call), and
+    the work plan of the batch at every share cut: few heavy requests (each cut into up to 16 shares), forced
+    cuts, the light wave first."""
+    ref, pol, ids = make("cpx")
+    reqs = pod_storm(ids, 600, seed=0xBA7C4)
+    want = [ref.Allocate(*r) for r in reqs]
+    results = [None, None]
+
+    def run(slot):
+        results[slot] = tp.allocate_batch(pol, reqs)[0]
+
+    threads = [threading.Thread(target=run, args=(t,)) for t in range(2)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert results[0] == want and results[1] == want
+    heavy = [r for r in reqs if r[2] == 8 and len(r[0]) >= 40][:12] + reqs[:20]
+    want_heavy = [ref.Allocate(*r) for r in heavy]
+    for shift, ipw, light_first in ((0, 0, False), (20, 2, False), (22, 16, True), (30, 1, False)):
+        pol.set_batch_tuning(share_shift=shift, items_per_warp=ipw, light_first=light_first)
+        got, infos = tp.allocate_batch(pol, heavy)
+        assert got == want_heavy, (shift, ipw, light_first)
+        for r, info in zip(heavy, infos):
+            if info["searched"]:
+                assert info["subsets_scored"] == info["subsets_total"], (shift, r)
+    pol.close()
+
+
 def test_concurrent_callers():
     """8 threads on one policy (grpc-go serves each RPC on its own goroutine, dpm/plugin.go:108-111)."""
     ref, pol, ids = make("mi308")
