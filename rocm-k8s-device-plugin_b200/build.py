@@ -19,7 +19,7 @@ TAG = os.environ.get("TP_BUILD_TAG", "")
 OBJ = os.path.join("/tmp", "tpalloc_build_" + TAG) if TAG else os.path.join(HERE, "build")  # (tagged objects stay out of the tree)
 LIB = os.path.join(HERE, "libtpalloc" + ("_" + TAG if TAG else "") + ".so")
 SPLIT_UNITS = [f"csrc/tp_split_m{m}_d{d}.cu" for m in (128, 96, 80, 64) for d in (4, 3, 2, 1, 0)]  # slowest first
-TRI_UNITS = [f"csrc/tp_tri_m{m}_d{d}.cu" for m in (80, 64) for d in (3, 2, 1, 0)]
+TRI_UNITS = [f"csrc/tp_tri_m{m}_d{d}.cu" for m in (80, 64) for d in (3, 2, 1)]
 SOURCES = TRI_UNITS + SPLIT_UNITS + ["csrc/tp_abi.cu", "csrc/tp_kernels.cu", "host/besteffort_policy.cpp"]
 HEADERS = ["csrc/tp_common.cuh", "csrc/tp_kernels.cuh", "csrc/tp_device.cuh", "csrc/tp_split.cuh", "csrc/tp_tri.cuh",
            "host/besteffort_policy.h"]

@@ -289,7 +289,7 @@ bool build_plan(const tp_policy *p, Prep &out) {
     if (p->tune_q) q = std::max(2, std::min({p->tune_q, k - 1, TP_SPLIT_MAX_D + 2})); // tuning aid
     int pp = k - q, tri_gcap = 0;
     if (k >= 6 && p->kernel != TP_KERNEL_SPLIT && !p->tune_q) {
-        const int tq = std::max(3, std::min(k - 4, TP_TRI_MAX_DW + 3)), tpp = k - tq;
+        const int tq = std::max(4, std::min(k - 4, TP_TRI_MAX_DW + 3)), tpp = k - tq; // >= 1 walked position
         if (tpp <= TP_SPLIT_MAX_P && n - tpp >= tq && (tri_gcap = tp_tri_fit(n, k, tpp, tq)) > 0) {
             q = tq;
             pp = tpp;
@@ -339,18 +339,31 @@ bool build_plan(const tp_policy *p, Prep &out) {
     // when one value alone is more than a quarter of what a lane has to do in this search (shard);
     // restricted b1 ranges lose the compile-time leaf blocks and add per-item set-up.
     pl.b_star = TP_MAX_N + 1;
+    const bool pair_b0 = tri_gcap > 0 && q == 4; // kernel TRI pairs the values of its one walked position (tp_split_bstar)
     if (q > 3) {
         const u64 lanes = (u64)p->sm_count * 2 * TP_SPLIT_THREADS;
         u64 cap1 = std::max<u64>(cap0, rq.total / (lanes * (u64)std::max(out.shards, 1) * 4));
         if (out.batch) cap1 = std::max<u64>(cap0, rq.total / (batch_lanes * 4));
         if (p->tune_cap1) cap1 = std::max<u64>(64, p->tune_cap1); // tuning aid
+        // (pairs: from a quarter of the cap on, so that the equal-work pieces below b_star are made of grains well
+        // below their target -- a piece of two pairs where one was meant is the longest item of the search)
         int bs = q - 1;
-        while (bs < n && p->binom[bs][q - 1] <= cap1) bs++;
+        while (bs < n && (pair_b0 ? 8 * p->binom[bs][q - 1] : p->binom[bs][q - 1]) <= cap1) bs++;
         pl.b_star = bs;
         pl.cum[bs] = 0;
-        for (int b = bs; b <= n && b <= TP_MAX_N; b++) {
-            const u64 nsub = std::min<u64>(std::max<u64>((p->binom[b][q - 1] + cap1 - 1) / cap1, 1), TP_SPLIT_MAX_SUB);
-            pl.cum[b + 1] = (uint16_t)(pl.cum[b] + nsub);
+        if (pair_b0) {
+            pl.cum[bs + 1] = 0;
+            if (bs + 2 <= TP_MAX_N + 1) pl.cum[bs + 2] = 0;
+            for (int b = bs + 1; b + 2 <= TP_MAX_N + 1; b++) { // head b of the pair (b, b - 1)
+                const u64 work = b <= n ? p->binom[b][q - 1] + p->binom[b - 1][q - 1] : 0;
+                const u64 nsub = std::min<u64>(std::max<u64>((work + cap1 - 1) / cap1, 1), TP_SPLIT_MAX_SUB);
+                pl.cum[b + 2] = (uint16_t)(pl.cum[b] + nsub);
+            }
+        } else {
+            for (int b = bs; b <= n && b <= TP_MAX_N; b++) {
+                const u64 nsub = std::min<u64>(std::max<u64>((p->binom[b][q - 1] + cap1 - 1) / cap1, 1), TP_SPLIT_MAX_SUB);
+                pl.cum[b + 1] = (uint16_t)(pl.cum[b] + nsub);
+            }
         }
     }
     u64 items = 0;
@@ -360,9 +373,10 @@ bool build_plan(const tp_policy *p, Prep &out) {
         const u64 chunks = (na + 31) / 32;
         if (chunks == 0 || chunks > 0xFFFFFFFFull) return false;
         int np = 1; // slices of the first walked position, each about `cap0` subsets per lane
-        const int jlow = std::min(jt, (int)pl.b_star);
+        const int jlow = std::min(jt, tp_split_bstar(jt, (int)pl.b_star, pair_b0));
         if (q > 2) np = (int)std::min<u64>(std::max<u64>((p->binom[jlow][q] + cap0 - 1) / cap0, 1), TP_SPLIT_MAX_PIECES);
-        const u64 top = jt > pl.b_star ? pl.cum[jt] : 0; // sub-slices of the single values b_star .. jt-1
+        auto cum = [&](int b) -> int { return pl.cum[b]; };
+        const u64 top = (u64)tp_split_top_slices(cum, jt, (int)pl.b_star, pair_b0); // parts of the single values (pairs)
         pl.item_base[e] = (uint32_t)items;
         pl.n_chunks[e] = (uint32_t)chunks;
         pl.n_pieces[e] = (uint8_t)np;
@@ -559,14 +573,14 @@ u64 shard_subsets(const tp_policy *p, const Prep &pr, int idx, int cnt) {
         auto Cb = [&](int a, int b) -> u64 { return p->binom[a][b]; };
         auto cum = [&](int b) -> int { return pl.cum[b]; };
         const int np = pl.n_pieces[e];
-        const int n_slices = np + (jt > pl.b_star ? pl.cum[jt] : 0);
+        const bool pair = pr.kernel == TP_KERNEL_TRI;
+        const int n_slices = np + tp_split_top_slices(cum, jt, (int)pl.b_star, pair && pl.q == 4);
         for (int slice = 0; slice < n_slices; slice++) {
             TpSlice sl;
             u64 per_lane = p->binom[jt][2]; // q == 2: every pair below the pivot
             if (pl.q > 2) {
-                if (!tp_split_slice(Cb, cum, jt, pl.q, np, pl.b_star, slice, sl)) continue;
-                per_lane = sl.cut_again ? p->binom[sl.b1_hi][pl.q - 1] - p->binom[sl.b1_lo][pl.q - 1]
-                                        : p->binom[sl.b0_hi][pl.q] - p->binom[sl.b0_lo][pl.q];
+                if (!tp_split_slice(Cb, cum, jt, pl.q, np, pl.b_star, slice, sl, pair)) continue;
+                per_lane = tp_split_slice_count(Cb, sl, pl.q);
             }
             for (u64 ac = 0; ac < pl.n_chunks[e]; ac++) {
                 const u64 item = pl.item_base[e] + (u64)slice * pl.n_chunks[e] + ac;

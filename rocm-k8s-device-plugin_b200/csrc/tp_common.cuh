@@ -174,33 +174,87 @@ struct TpSlice {
 // Slice i of np of the first walked position b0 in [q-1, jt): boundaries put about the same number
 // of subsets (C(b,q) counts those with b0 < b) in every slice; a slice can be empty, since one
 // b0 value is the finest grain.  Used by the kernel (item -> slice) and by the host (counting).
+// pair (kernel TRI, which takes the values of its last walked position two at a time from the top): an inner
+// boundary keeps an even distance to the top of the range, so that only the lowest slice can end on a single value.
 template <class BinomFn>
-__host__ __device__ inline int tp_split_cut(BinomFn C, int jt, int q, int np, int i) {
+__host__ __device__ inline int tp_split_cut(BinomFn C, int jt, int q, int np, int i, bool pair = false) {
     if (i <= 0) return q - 1;
     if (i >= np) return jt;
-    const unsigned long long target = C(jt, q) * (unsigned long long)i / (unsigned long long)np;
+    const unsigned long long tot = C(jt, q); // (a 32-bit division where it fits: this runs once per work item)
+    const unsigned long long target = (tot >> 25) ? tot * (unsigned long long)i / (unsigned long long)np
+                                                  : (unsigned long long)((unsigned)tot * (unsigned)i / (unsigned)np);
     int lo = q - 1, hi = jt; // smallest b with C(b,q) >= target
     while (lo < hi) {
         const int mid = (lo + hi) >> 1;
         if (C(mid, q) >= target) hi = mid;
         else lo = mid + 1;
     }
+    if (pair && ((jt - lo) & 1)) lo++;
     return lo;
+}
+
+// Subsets per lane in a slice (q positions below the lane set).
+template <class BinomFn>
+__host__ __device__ inline unsigned long long tp_split_slice_count(BinomFn C, const TpSlice &sl, int q) {
+    if (!sl.cut_again) return C(sl.b0_hi, q) - C(sl.b0_lo, q);
+    unsigned long long sum = 0; // every first value of the slice, cut by the position below it
+    for (int b0 = sl.b0_lo; b0 < sl.b0_hi; b0++) {
+        const int hi = sl.b1_hi < b0 ? sl.b1_hi : b0, lo = sl.b1_lo < b0 ? sl.b1_lo : b0;
+        sum += C(hi, q - 1) - C(lo, q - 1);
+    }
+    return sum;
+}
+
+// Kernel TRI with one walked position (q == 4) takes that position's values two at a time, so there the values at
+// and above b_star become items in PAIRS (b, b - 1), b = jt - 1, jt - 3, ...: the pairs start at b_star or one above
+// it, whichever leaves an even number of values below the pivot, and cum() sums the parts of the pair heads of
+// one parity (cum(b + 2) = cum(b) + parts of head b).
+__host__ __device__ inline int tp_split_bstar(int jt, int b_star, bool pair_b0) {
+    if (!pair_b0 || jt <= b_star) return b_star;
+    return b_star + ((jt - b_star) & 1);
+}
+// Slices of pivot jt beyond its np pieces: the parts of the single values (pairs) [b_star, jt).
+template <class CumFn>
+__host__ __device__ inline int tp_split_top_slices(CumFn cum, int jt, int b_star, bool pair_b0) {
+    if (pair_b0) return jt - tp_split_bstar(jt, b_star, true) >= 2 ? (int)cum(jt + 1) : 0;
+    return jt > b_star ? (int)cum(jt) : 0;
 }
 
 // Slice number -> ranges of the first two walked positions; false when the slice is empty.
 // Shared by the kernel (item -> work) and the host (counting what a shard scores).
 template <class BinomFn, class CumFn>
 __host__ __device__ inline bool tp_split_slice(BinomFn C, CumFn cum, int jt, int q, int np, int b_star, int slice,
-                                               TpSlice &o) {
+                                               TpSlice &o, bool pair = false) {
     o.b1_lo = 0;
     o.b1_hi = TP_MAX_N;
     o.cut_again = false;
+    const bool pair_b0 = pair && q == 4;
+    const int b_eff = tp_split_bstar(jt, b_star, pair_b0);
     if (slice < np) {
-        const int jlow = jt < b_star ? jt : b_star;
-        o.b0_lo = tp_split_cut(C, jlow, q, np, slice);
-        o.b0_hi = tp_split_cut(C, jlow, q, np, slice + 1);
+        const int jlow = jt < b_eff ? jt : b_eff;
+        o.b0_lo = tp_split_cut(C, jlow, q, np, slice, pair);
+        o.b0_hi = tp_split_cut(C, jlow, q, np, slice + 1, pair);
         return o.b0_lo < o.b0_hi;
+    }
+    if (pair_b0) {
+        const int t = slice - np;
+        int lo = 0, hi = (jt - b_eff) >> 1; // heads b_eff + 1 + 2 i: the largest i with cum(head) <= t
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if ((int)cum(b_eff + 1 + 2 * mid) <= t) lo = mid;
+            else hi = mid;
+        }
+        const int b = b_eff + 1 + 2 * lo;
+        const int nsub = (int)cum(b + 2) - (int)cum(b), sub = t - (int)cum(b);
+        o.b0_lo = b - 1;
+        o.b0_hi = b + 1;
+        if (nsub > 1) { // cut by the position below the pair: the top of the triple
+            o.b1_lo = tp_split_cut(C, b, q - 1, nsub, sub);
+            o.b1_hi = tp_split_cut(C, b, q - 1, nsub, sub + 1);
+            o.cut_again = true;
+            return o.b1_lo < o.b1_hi;
+        }
+        return true;
     }
     const int t = slice - np;
     int lo = b_star, hi = jt; // largest b in [b_star, jt) with cum(b) <= t
@@ -213,8 +267,8 @@ __host__ __device__ inline bool tp_split_slice(BinomFn C, CumFn cum, int jt, int
     o.b0_lo = lo;
     o.b0_hi = lo + 1;
     if (nsub > 1) {
-        o.b1_lo = tp_split_cut(C, lo, q - 1, nsub, sub);
-        o.b1_hi = tp_split_cut(C, lo, q - 1, nsub, sub + 1);
+        o.b1_lo = tp_split_cut(C, lo, q - 1, nsub, sub, pair);
+        o.b1_hi = tp_split_cut(C, lo, q - 1, nsub, sub + 1, pair);
         o.cut_again = true;
         return o.b1_lo < o.b1_hi;
     }

@@ -467,11 +467,10 @@ cudaError_t tp_launch_batch_split(const uint8_t *d_weight, int n_devices, const 
 }
 
 // Kernel TRI: lane vectors of 64 or 80 positions, 0..3 walked positions above the triple.
-#define TP_TRI_MAX_DYN_SMEM (232448 - 6144) /* 227 KB per block minus the kernel's static shared memory */
+#define TP_TRI_MAX_DYN_SMEM (232448 - 12288) /* 227 KB per block minus the kernel's static shared memory (10.5 KB) */
 static size_t tp_tri_smem(int need, int DW, int n, int k, int gcap) {
 #define TP_TRI_SMEM_BY_DEPTH(M)                          \
     switch (DW) {                                        \
-    case 0: return tp_tri_smem_m##M##_d0(n, k, gcap);    \
     case 1: return tp_tri_smem_m##M##_d1(n, k, gcap);    \
     case 2: return tp_tri_smem_m##M##_d2(n, k, gcap);    \
     case 3: return tp_tri_smem_m##M##_d3(n, k, gcap);    \
@@ -485,8 +484,8 @@ static size_t tp_tri_smem(int need, int DW, int n, int k, int gcap) {
 
 int tp_tri_fit(int n, int k, int p, int q) {
     const int DW = q - 3, need = n - p;
-    if (DW < 0 || DW > TP_TRI_MAX_DW || need > TP_TRI_MAX_M || p < 1) return 0;
-    // the top of the triple reaches need - 1 - DW; leaf b belongs to pair (b - 1) / 2
+    if (DW < 1 || DW > TP_TRI_MAX_DW || need > TP_TRI_MAX_M || p < 1) return 0; // (the last walked level pairs its values)
+    // the top of the triple reaches need - 1 - DW; leaves up to 2 gcap get a table
     int gcap = (need - 1 - DW - 1) / 2 + 1;
     if (gcap > tp_tri_gc()) gcap = tp_tri_gc(); // the lane registers hold 2 TP_TRI_GC positions
     while (gcap >= 4 && tp_tri_smem(need, DW, n, k, gcap) > TP_TRI_MAX_DYN_SMEM) gcap--;
@@ -501,7 +500,6 @@ static cudaError_t tp_dispatch_tri(int DW, int need, const uint8_t *d_weight, in
     d_weight, n_devices, d_binom, d_rq, h, d_plan, gcap, shard_idx, shard_cnt, sc, d_counter, sm_count, st, info, batch
 #define TP_TRI_BY_DEPTH(M)                                 \
     switch (DW) {                                          \
-    case 0: return tp_launch_tri_m##M##_d0(TP_TRI_ARGS);   \
     case 1: return tp_launch_tri_m##M##_d1(TP_TRI_ARGS);   \
     case 2: return tp_launch_tri_m##M##_d2(TP_TRI_ARGS);   \
     case 3: return tp_launch_tri_m##M##_d3(TP_TRI_ARGS);   \

@@ -60,7 +60,7 @@ cudaError_t tp_launch_batch_tri(const uint8_t *d_weight, int n_devices, const un
 // Largest table cap (leaf pairs) whose shared memory fits beside everything else the kernel stages for a
 // request with n free devices, k' = k, |A| = p and q positions below the lane set; 0 = kernel TRI cannot run.
 int tp_tri_fit(int n, int k, int p, int q);
-int tp_tri_gc(); // TP_TRI_GC of the build (defined next to the kernel, tp_tri_m64_d0.cu)
+int tp_tri_gc(); // TP_TRI_GC of the build (defined next to the kernel, tp_tri_m64_d1.cu)
 #define TP_DECLARE_TRI_LAUNCHER(M, D)                                                                            \
     cudaError_t tp_launch_tri_m##M##_d##D(const uint8_t *W, int nd, const unsigned long long *binom,            \
                                           const TpReq *d_rq, const TpReq &h, const TpPlan *d_plan, int gcap,    \
@@ -68,7 +68,7 @@ int tp_tri_gc(); // TP_TRI_GC of the build (defined next to the kernel, tp_tri_m
                                           cudaStream_t st, TpLaunchInfo *info, const TpBatch &batch);           \
     size_t tp_tri_smem_m##M##_d##D(int n, int k, int gcap);
 #define TP_DECLARE_TRI_LAUNCHERS(M) \
-    TP_DECLARE_TRI_LAUNCHER(M, 0) TP_DECLARE_TRI_LAUNCHER(M, 1) TP_DECLARE_TRI_LAUNCHER(M, 2) TP_DECLARE_TRI_LAUNCHER(M, 3)
+    TP_DECLARE_TRI_LAUNCHER(M, 1) TP_DECLARE_TRI_LAUNCHER(M, 2) TP_DECLARE_TRI_LAUNCHER(M, 3)
 TP_DECLARE_TRI_LAUNCHERS(64)
 TP_DECLARE_TRI_LAUNCHERS(80)
 

@@ -1,5 +1,5 @@
 // tp_tri.cuh -- kernel TRI: the exhaustive scorer for k' >= 6 on up to 80 + p free devices.
-// Included by tp_tri_m*_d*.cu, one translation unit per (lane-vector width M, walked depth DW).
+// Included by tp_tri_m*_d*.cu, one translation unit per (lane-vector width M, walked depth DW >= 1).
 //
 // Same contract and the same outer structure as kernel SPLIT (tp_split.cuh): positions are the
 // canonical order reversed, a subset is j_1 > ... > j_k'; the top p positions A belong to a LANE
@@ -15,23 +15,28 @@
 //
 //     score(A, walked, b, jx, jy) = base + VT[b] + VT[jx] + VT[jy] + S3[b][jx][jy].
 //
-// Layout that makes one row cost nothing beyond its pairs: rows jx = 2h and 2h+1 of leaf b are
-// interleaved in one 32-bit word per jy (low half: row 2h, high half: row 2h+1; TP_BIG where
-// jy >= jx or the row does not exist), and the lane keeps VT[jy] SPLATTED (the same 16-bit value in
-// both halves of a register, one register per position).  Then
+// The two 16-bit halves of every lane register belong to TWO PREFIXES: the last walked position
+// takes the values b0 and b0 - 1 at once (VT.lo = V + T(.., b0), VT.hi = V + T(.., b0 - 1)), and a
+// table word holds the same S3 entry in both halves.  Then, for leaf b and row jx,
 //
-//     acc = min(acc, VT[jy] + word(h, jy))        one VIADDMNMX.U16x2 = two subsets, for jy <= 2h
-//     run = min(run, acc + (VT[2h] | VT[2h+1] << 16))   ONE closing op for TWO rows (+ one PRMT)
+//     acc = min(acc, VT[jy] + word(b, jx, jy))     one VIADDMNMX.U16x2 = the same triple for both prefixes
+//     run = min(run, acc + VT[jx])                 the closing op of the row: no repacking of anything
 //
-// where SPLIT pays a PRMT and a VIADDMNMX per row, and an odd row wastes half an op only once per
-// row pair.  Leaves 2g+1 and 2g+2 have the same row pairs 0..g and are scored in one pass: two
-// independent chains off the same lane registers, two table rows per load group.
+// Every prefix-level cost (the T update, building VT, the leaf loop's set-up and tests) is paid once per
+// two prefixes, rows are exactly as long as they are (no interleaved row pairs with a diagonal and a missing
+// half), and a leaf is a pass of its own (no pairs of leaves with an odd one out).  Leaf b0 - 1 exists for the
+// first prefix only: T(.., b0 - 1) holds TP_BIG at position b0 - 1, which keeps the other half out of every
+// minimum.  A last single value of the walked range runs with its upper half switched off (threshold 0).
 //
-// Shared memory decides how many leaves get a table: 2 * sum_{g<G} off(g+1) 16-byte chunks, 100 KB
-// for G = 32 (leaves 1..64, which is every leaf for n - p <= 67).  Leaves above the cap (0.06 % of
-// the subsets of the 8-of-80 search) go to the exact scalar re-walk that also serves candidates
-// (tp_split_slow), which prunes whole rows against the bound.
+// A leaf's table is its rows 1 .. b-1 back to back (row jx: jx words at word C(jx,2)); rows are consumed in
+// pairs (2H+1, 2H), top down, as two independent chains.  An odd leaf has no row b = 2H+1 in its top pair: b
+// words of TP_BIG follow its table, so that the pair's code needs no special case.
+//
+// Shared memory decides how many leaves get a table: C(L+1,3) words for leaves up to L, 76 KB for L = 48
+// (every leaf for n - p <= 50).  Leaves above the cap (0.06 % of the subsets of the 8-of-80 search) go to
+// the exact scalar re-walk that also serves candidates (tp_split_slow), which prunes whole rows against the bound.
 #pragma once
+#include <type_traits>
 #include "tp_split.cuh"
 
 #ifndef TP_TRI_WARPS
@@ -39,24 +44,31 @@
 #endif
 #define TP_TRI_THREADS (TP_TRI_WARPS * 32)
 #ifndef TP_TRI_GC
-#define TP_TRI_GC 24 /* leaf pairs with a table, at most: rows below 2 GC -> 2 GC lane registers */
+#define TP_TRI_GC 24 /* row pairs with code: leaves up to 2 GC have a table, positions below 2 GC a lane register */
 #endif
 #define TP_TRI_NREG (2 * TP_TRI_GC)
+#define TP_TRI_LMAX (2 * TP_TRI_GC) /* the largest leaf with a table, at most */
 
-
-// Row pair h of a leaf's table holds entries jy = 0..2h, padded to 16-byte chunks of four.
-__host__ __device__ constexpr int tp_tri_chunks(int h) { return (h >> 1) + 1; }
-// ... and starts at this chunk: sum of tp_tri_chunks(h') over h' < h.
-__host__ __device__ constexpr int tp_tri_off(int h) {
-    return (h & 1) ? ((h >> 1) + 1) * ((h >> 1) + 1) : (h >> 1) * ((h >> 1) + 1);
-}
-// Leaves 2g+1 and 2g+2 both have row pairs 0..g, tp_tri_off(g+1) chunks each; pair g starts here.
-__host__ __device__ constexpr int tp_tri_pair_base(int g) {
+__host__ __device__ constexpr int tp_tri_c2(int x) { return x * (x - 1) / 2; }
+// Words of leaf b's table: rows 1 .. b-1, b words of TP_BIG after an odd leaf, rounded up to 16 bytes.
+__host__ __device__ constexpr int tp_tri_leaf_words(int b) { return (tp_tri_c2(b) + ((b & 1) ? b : 0) + 3) & ~3; }
+// ... and where it starts (in words): leaves 2, 3, ... back to back.
+__host__ __device__ constexpr int tp_tri_leaf_off(int b) {
     int s = 0;
-    for (int i = 0; i < g; i++) s += tp_tri_off(i + 1);
-    return 2 * s;
+    for (int i = 2; i < b; i++) s += tp_tri_leaf_words(i);
+    return s;
 }
-static __host__ __device__ inline size_t tp_tri_table_bytes(int gcap) { return (size_t)tp_tri_pair_base(gcap) * 16; }
+static __host__ __device__ inline size_t tp_tri_table_bytes(int gcap) { return (size_t)tp_tri_leaf_off(2 * gcap + 1) * 4; }
+// Row jx inside a leaf: 16-byte chunks c0 .. c1 hold its words (the first and the last one shared with its neighbours).
+__host__ __device__ constexpr int tp_tri_row_c0(int jx) { return tp_tri_c2(jx) / 4; }
+__host__ __device__ constexpr int tp_tri_row_nch(int jx) { return jx < 1 ? 0 : (tp_tri_c2(jx) + jx - 1) / 4 - tp_tri_row_c0(jx) + 1; }
+// Rows of one parity form a stream of chunks, top row first; this is where row jx's first chunk stands in it
+// (its low bit picks the buffer of the software pipeline below).
+__host__ __device__ constexpr int tp_tri_row_seq(int jx) {
+    int s = 0;
+    for (int r = jx + 2; r < TP_TRI_LMAX; r += 2) s += tp_tri_row_nch(r);
+    return s;
+}
 
 // Shared-memory loads by 32-bit shared address + immediate: the hot function is not inlined, and
 // a generic pointer handed across a call would turn every table load into a 64-bit generic LD.
@@ -81,152 +93,102 @@ __device__ __forceinline__ unsigned tp_lds16(unsigned addr) {
     return v;
 }
 
-// Two "acc = min(acc, vt + word)" steps.  With TP_TRI_MIN3 they are IMAD + IMAD + VIMNMX3.U16x2: the adds go to
-// the FMA pipe (a multiply by a register that holds 1 keeps ptxas from turning them back into ALU adds) and the
-// half-rate ALU pipe sees one instruction for two steps instead of two VIADDMNMX.  As a microbenchmark that is
-// 1.77 x the add-min rate (scripts/int_peaks.py, variants 6 / 7: 16.4 T against 29.0 T steps/s); in this kernel
-// it is 12-17 % SLOWER (8 of 64: 0.358 against 0.321 ms, 8 of 80: 1.86 against 1.58 ms): three issue slots
-// for two steps instead of two, and the kernel as a whole is short of issue slots, not of ALU cycles.  Off.
-#ifndef TP_TRI_MIN3
-#define TP_TRI_MIN3 0
-#endif
-__device__ __forceinline__ unsigned tp_step2(unsigned acc, unsigned v0, unsigned w0, unsigned v1, unsigned w1, unsigned one) {
-#if TP_TRI_MIN3
-    unsigned t0, t1;
-    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t0) : "r"(w0), "r"(one), "r"(v0));
-    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t1) : "r"(w1), "r"(one), "r"(v1));
-    return __vimin3_u16x2(t0, t1, acc);
-#else
-    (void)one;
-    return __viaddmin_u16x2(v1, w1, __viaddmin_u16x2(v0, w0, acc));
-#endif
-}
-
-// One row pair of both leaves of a pass.  H is a compile-time constant: every register index and
-// every table offset below is an immediate.  tA, tB: shared addresses of the two leaves' tables.
-template <int H>
-__device__ __forceinline__ void tp_tri_rowpair(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                               unsigned &runA, unsigned &runB, unsigned one) {
-    constexpr int NCH = tp_tri_chunks(H), OFF = tp_tri_off(H);
-    unsigned accA = TP_BIG2 + TP_BIG2, accB = TP_BIG2 + TP_BIG2;
-#pragma unroll
-    for (int c = 0; c < NCH; c++) {
-        const uint4 a = tp_lds128(tA + (OFF + c) * 16), b = tp_lds128(tB + (OFF + c) * 16);
-        if (4 * c + 1 <= 2 * H) {
-            accA = tp_step2(accA, VT[4 * c + 0], a.x, VT[4 * c + 1], a.y, one);
-            accB = tp_step2(accB, VT[4 * c + 0], b.x, VT[4 * c + 1], b.y, one);
-        } else {
-            accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
-        }
-        if (4 * c + 3 <= 2 * H) {
-            accA = tp_step2(accA, VT[4 * c + 2], a.z, VT[4 * c + 3], a.w, one);
-            accB = tp_step2(accB, VT[4 * c + 2], b.z, VT[4 * c + 3], b.w, one);
-        } else if (4 * c + 2 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 2], a.z, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 2], b.z, accB);
-        }
+// f(integral_constant<int, I>) for I in [I0, I1): compile-time indices for registers and table offsets
+template <int I0, int I1, class F>
+__device__ __forceinline__ void tp_static_for(F &&f) {
+    if constexpr (I0 < I1) {
+        f(std::integral_constant<int, I0>{});
+        tp_static_for<I0 + 1, I1>(f);
     }
-    const unsigned pk = __byte_perm(VT[2 * H], VT[2 * H + 1], 0x5410); // VT[2H] | VT[2H+1] << 16
-    runA = __viaddmin_u16x2(accA, pk, runA);
-    runB = __viaddmin_u16x2(accB, pk, runB);
 }
 
-// The generic pass enters its rows through a switch, so every row pair is a basic block of its
-// own and the compiler cannot start a row pair's loads during the one before it.  With
-// TP_TRI_PREFETCH the first chunk of row pair H - 1 (both leaves) is loaded by hand while row pair H
-// computes, into two alternating pairs of buffers.
-#ifndef TP_TRI_PREFETCH
-#define TP_TRI_PREFETCH 1
-#endif
-// Chunks are consumed row pair by row pair (H descending, c ascending); chunk (H, c) sits in buffer
-// set (S(H) + c) & 1, S(H) = chunks of the row pairs above H, so that consecutive chunks alternate.
-__host__ __device__ constexpr int tp_tri_buf(int h, int c) {
-    return (tp_tri_off(TP_TRI_GC) - tp_tri_off(h + 1) + c) & 1;
+// The words of chunk C (of a leaf's table) that belong to row JX, against the lane registers.
+template <int JX, int C>
+__device__ __forceinline__ void tp_tri_row_chunk(const unsigned (&VT)[TP_TRI_NREG], const uint4 &q, unsigned &acc) {
+    constexpr int J0 = 4 * C - tp_tri_c2(JX); // jy of the chunk's first word
+    if constexpr (J0 + 0 >= 0 && J0 + 0 < JX) acc = __viaddmin_u16x2(VT[J0 + 0], q.x, acc);
+    if constexpr (J0 + 1 >= 0 && J0 + 1 < JX) acc = __viaddmin_u16x2(VT[J0 + 1], q.y, acc);
+    if constexpr (J0 + 2 >= 0 && J0 + 2 < JX) acc = __viaddmin_u16x2(VT[J0 + 2], q.z, acc);
+    if constexpr (J0 + 3 >= 0 && J0 + 3 < JX) acc = __viaddmin_u16x2(VT[J0 + 3], q.w, acc);
 }
-__device__ __forceinline__ unsigned tp_pack_lo(unsigned a, unsigned b) { // a.lo | b.lo << 16; volatile: computed
-    unsigned r;                                                          // where it stands, not hoisted out of the
-    asm volatile("prmt.b32 %0, %1, %2, 0x5410;" : "=r"(r) : "r"(a), "r"(b)); // pass loop into 24 more registers
-    return r;
+
+// One row of a leaf whose table starts at shared address tl, loads where they are needed (the
+// straight-line small leaves: the compiler schedules across rows and leaves).
+template <int JX>
+__device__ __forceinline__ void tp_tri_row(const unsigned (&VT)[TP_TRI_NREG], unsigned tl, unsigned &run) {
+    unsigned acc = TP_BIG2 + TP_BIG2;
+    tp_static_for<0, tp_tri_row_nch(JX)>([&](auto ic) {
+        constexpr int C = tp_tri_row_c0(JX) + decltype(ic)::value;
+        const uint4 q = tp_lds128(tl + C * 16);
+        tp_tri_row_chunk<JX, C>(VT, q, acc);
+    });
+    run = __viaddmin_u16x2(acc, VT[JX], run);
 }
+
+// Rows 2H+1 (chain A) and 2H (chain B) of the leaf at tl, software-pipelined: the generic pass enters its rows
+// through a switch, so every row pair is a basic block of its own and the compiler cannot start a row pair's
+// loads during the one before it.  Each chain keeps two buffers; chunk i of row jx sits in buffer
+// (tp_tri_row_seq(jx) + i) & 1 and the next chunk of the chain (of this row, or the first of row jx - 2) is
+// loaded by hand before this one is used.
 template <int H>
-__device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                                  unsigned &runA, unsigned &runB, uint4 (&bA)[2], uint4 (&bB)[2],
-                                                  unsigned one) {
-    constexpr int NCH = tp_tri_chunks(H), OFF = tp_tri_off(H);
+__device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NREG], unsigned tl, unsigned &runA,
+                                                  unsigned &runB, uint4 (&bA)[2], uint4 (&bB)[2]) {
+    constexpr int JA = 2 * H + 1, JB = 2 * H;
+    constexpr int NA = tp_tri_row_nch(JA), NB = tp_tri_row_nch(JB);
+    constexpr int SA = tp_tri_row_seq(JA), SB = tp_tri_row_seq(JB);
     unsigned accA = TP_BIG2 + TP_BIG2, accB = TP_BIG2 + TP_BIG2;
-#pragma unroll
-    for (int c = 0; c < NCH; c++) {
-        constexpr int dummy = 0;
-        (void)dummy;
-        const int cur = tp_tri_buf(H, c);
-        // the next chunk (of this row pair, or the first of the one below) starts before this one is used
-        if (c + 1 < NCH) {
-            bA[cur ^ 1] = tp_lds128v(tA + (OFF + c + 1) * 16);
-            bB[cur ^ 1] = tp_lds128v(tB + (OFF + c + 1) * 16);
-        } else if (H > 0) {
-            bA[cur ^ 1] = tp_lds128v(tA + tp_tri_off(H > 0 ? H - 1 : 0) * 16);
-            bB[cur ^ 1] = tp_lds128v(tB + tp_tri_off(H > 0 ? H - 1 : 0) * 16);
+    tp_static_for<0, (NA > NB ? NA : NB)>([&](auto ic) {
+        constexpr int I = decltype(ic)::value;
+        if constexpr (I < NA) {
+            constexpr int CUR = (SA + I) & 1;
+            if constexpr (I + 1 < NA) bA[CUR ^ 1] = tp_lds128v(tl + (tp_tri_row_c0(JA) + I + 1) * 16);
+            else if constexpr (H > 0) bA[CUR ^ 1] = tp_lds128v(tl + tp_tri_row_c0(JA - 2) * 16);
+            tp_tri_row_chunk<JA, tp_tri_row_c0(JA) + I>(VT, bA[CUR], accA);
         }
-        const uint4 a = bA[cur], b = bB[cur];
-        if (4 * c + 1 <= 2 * H) {
-            accA = tp_step2(accA, VT[4 * c + 0], a.x, VT[4 * c + 1], a.y, one);
-            accB = tp_step2(accB, VT[4 * c + 0], b.x, VT[4 * c + 1], b.y, one);
-        } else {
-            accA = __viaddmin_u16x2(VT[4 * c + 0], a.x, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 0], b.x, accB);
+        if constexpr (I < NB) {
+            constexpr int CUR = (SB + I) & 1;
+            if constexpr (I + 1 < NB) bB[CUR ^ 1] = tp_lds128v(tl + (tp_tri_row_c0(JB) + I + 1) * 16);
+            else if constexpr (H > 1) bB[CUR ^ 1] = tp_lds128v(tl + tp_tri_row_c0(JB - 2) * 16);
+            tp_tri_row_chunk<JB, tp_tri_row_c0(JB) + I>(VT, bB[CUR], accB);
         }
-        if (4 * c + 3 <= 2 * H) {
-            accA = tp_step2(accA, VT[4 * c + 2], a.z, VT[4 * c + 3], a.w, one);
-            accB = tp_step2(accB, VT[4 * c + 2], b.z, VT[4 * c + 3], b.w, one);
-        } else if (4 * c + 2 <= 2 * H) {
-            accA = __viaddmin_u16x2(VT[4 * c + 2], a.z, accA);
-            accB = __viaddmin_u16x2(VT[4 * c + 2], b.z, accB);
-        }
-    }
-    const unsigned pk = tp_pack_lo(VT[2 * H], VT[2 * H + 1]); // VT[2H] | VT[2H+1] << 16
-    runA = __viaddmin_u16x2(accA, pk, runA);
-    runB = __viaddmin_u16x2(accB, pk, runB);
+    });
+    runA = __viaddmin_u16x2(accA, VT[JA], runA);
+    if constexpr (H > 0) runB = __viaddmin_u16x2(accB, VT[JB], runB);
 }
 
-#if TP_TRI_PREFETCH
-#define TP_TRI_CASE(H)                                                                               \
-    case H:                                                                                          \
-        tp_tri_rowpair_pf<(H)>(VT, tA, tB, runA, runB, bufA, bufB, one);                             \
+#define TP_TRI_CASE(H)                                              \
+    case H:                                                         \
+        tp_tri_rowpair_pf<(H)>(VT, tl, runA, runB, bufA, bufB);     \
         [[fallthrough]];
-#else
-#define TP_TRI_CASE(H)                                   \
-    case H:                                              \
-        tp_tri_rowpair<(H)>(VT, tA, tB, runA, runB, one);     \
-        [[fallthrough]];
-#endif
 #define TP_TRI_CASE8(B)                                                                          \
     TP_TRI_CASE(B + 7) TP_TRI_CASE(B + 6) TP_TRI_CASE(B + 5) TP_TRI_CASE(B + 4) TP_TRI_CASE(B + 3) \
     TP_TRI_CASE(B + 2) TP_TRI_CASE(B + 1) TP_TRI_CASE(B + 0)
 
-// Eight positions of VT = V + T, splatted.
+// Eight positions of VT: low halves V + T', high halves V + T'' (T'' stands TP_TRI_T2 bytes after T').
 template <int C>
-__device__ __forceinline__ void tp_tri_vt_chunk(unsigned (&VT)[TP_TRI_NREG], unsigned v4, unsigned t4) {
+__device__ __forceinline__ void tp_tri_vt_chunk(unsigned (&VT)[TP_TRI_NREG], unsigned v4, unsigned t4, unsigned t2_off) {
     const uint4 v = tp_lds128v(v4 + C * 512); // lane-private: [chunk][lane]
     const uint4 t = tp_lds128v(t4 + C * 16);
-    const unsigned x = v.x + t.x, y = v.y + t.y, z = v.z + t.z, w = v.w + t.w;
-    VT[8 * C + 0] = __byte_perm(x, 0, 0x1010);
-    VT[8 * C + 1] = __byte_perm(x, 0, 0x3232);
-    VT[8 * C + 2] = __byte_perm(y, 0, 0x1010);
-    VT[8 * C + 3] = __byte_perm(y, 0, 0x3232);
-    VT[8 * C + 4] = __byte_perm(z, 0, 0x1010);
-    VT[8 * C + 5] = __byte_perm(z, 0, 0x3232);
-    VT[8 * C + 6] = __byte_perm(w, 0, 0x1010);
-    VT[8 * C + 7] = __byte_perm(w, 0, 0x3232);
+    const uint4 s = tp_lds128v(t4 + t2_off + C * 16);
+    const unsigned x0 = v.x + t.x, x1 = v.y + t.y, x2 = v.z + t.z, x3 = v.w + t.w;
+    const unsigned y0 = v.x + s.x, y1 = v.y + s.y, y2 = v.z + s.z, y3 = v.w + s.w;
+    VT[8 * C + 0] = __byte_perm(x0, y0, 0x5410);
+    VT[8 * C + 1] = __byte_perm(x0, y0, 0x7632);
+    VT[8 * C + 2] = __byte_perm(x1, y1, 0x5410);
+    VT[8 * C + 3] = __byte_perm(x1, y1, 0x7632);
+    VT[8 * C + 4] = __byte_perm(x2, y2, 0x5410);
+    VT[8 * C + 5] = __byte_perm(x2, y2, 0x7632);
+    VT[8 * C + 6] = __byte_perm(x3, y3, 0x5410);
+    VT[8 * C + 7] = __byte_perm(x3, y3, 0x7632);
 }
-#define TP_TRI_VT_CASE(C)                  \
-    case (C) + 1:                          \
-        tp_tri_vt_chunk<(C)>(VT, va, tl);  \
+#define TP_TRI_VT_CASE(C)                           \
+    case (C) + 1:                                   \
+        tp_tri_vt_chunk<(C)>(VT, va, t1, 2u * M);   \
         [[fallthrough]];
 
 // What the hot loop does not need in registers lives here: the block's tables (written once per
 // request) and, per warp, the item it is on.  The slow path rebuilds its view from these, so that
-// the leaf loop carries the 64 lane registers and little else.
+// the leaf loop carries the lane registers and little else.
 // Phase timestamps of block 0 (tuning aid, compiled only with -DTP_TRI_TIMING; read by tp_tri_times_m<M>_d<D>).
 #ifdef TP_TRI_TIMING
 static __device__ unsigned long long tp_tri_times[16];
@@ -255,7 +217,7 @@ static __device__ unsigned long long tp_tri_times[16];
 struct TpTriBlock {
     TpSplitShared sh;
     TpSmem s;
-    const uint4 *tbl;       // the S3 table: leaf pairs 0..gcap-1
+    const uint32_t *tbl;    // the S3 table: leaves 2 .. 2 gcap
     const uint16_t *t0;     // u in reversed positions (level 0 of T)
     unsigned char *warp0;   // per-warp areas
     int per_warp;
@@ -265,14 +227,25 @@ struct TpTriBlock {
     unsigned *g_bound_inv; // see tp_tri_setup
 };
 static __shared__ TpTriBlock tp_tri_blk;
-static __shared__ int tp_tri_bound;                          // best Family score seen by the block
-static __shared__ uint16_t tp_tri_pair_start[TP_TRI_GC + 1]; // first chunk of every leaf pair
-// per leaf pair g, in bytes: table of leaf 2g+1, distance to the table of leaf 2g+2, first chunk of row pair g
-static __shared__ uint4 tp_tri_pair_info[TP_TRI_GC];
+static __shared__ int tp_tri_bound; // best Family score seen by the block
+// per leaf b, in bytes: its table, and inside it the first chunk of the two rows of its top pair (2H+1, 2H; H = (b-1)/2)
+static __shared__ uint4 tp_tri_leaf_info[TP_TRI_LMAX + 1];
 // the plan's per-pivot tables (item -> pivot lookups happen once per item)
 static __shared__ uint32_t tp_tri_item_base[TP_MAX_N], tp_tri_n_chunks[TP_MAX_N];
 static __shared__ uint8_t tp_tri_pieces[TP_MAX_N];
 static __shared__ uint16_t tp_tri_cum[TP_MAX_N + 2];
+// Slice boundaries, computed once per request (tp_split_cut costs a 64-bit division and a binary search, and an
+// item needs two of them): the np + 1 boundaries of pivot entry e start at tp_tri_cut_base[e]; the leaf cuts of the
+// pair with head b (one walked position: tp_split_bstar) are tp_tri_lcuts[b][0 .. parts].  tp_tri_cuts_ok == 0: the
+// boundaries did not fit, items compute theirs.
+#define TP_TRI_MAX_CUTS 1536
+#define TP_TRI_MAX_HEADS (TP_TRI_MAX_M + 8)
+static __shared__ uint16_t tp_tri_cut_base[TP_MAX_N + 1];
+static __shared__ uint8_t tp_tri_cuts[TP_TRI_MAX_CUTS];
+static __shared__ uint8_t tp_tri_lcuts[TP_TRI_MAX_HEADS][TP_SPLIT_MAX_SUB + 1];
+static __shared__ int tp_tri_cuts_ok;
+// C(m, i) for i = 1 .. 4, saturated: unranking a lane set of up to five positions in 32-bit arithmetic
+static __shared__ uint32_t tp_tri_c32[4][TP_MAX_N + 1];
 
 // byte area of a warp (32 bytes): [0..7] walked positions, [8], [9] bounds on the second position of
 // the item, [10] the item's pivot, [12..15] its chunk of lane sets, [16..23] subsets scored so far
@@ -306,20 +279,66 @@ __device__ __forceinline__ void tp_tri_unrank(BinomFn C, int mA, int p, int jt, 
     else a1 |= (u64)jt << (8 * (cnt - 8));
 }
 
-// The exact re-walk of one leaf for this lane (candidates, and leaves without a table): everything
-// it needs is read back from shared memory, the lane's A is unranked again.
+// The same for p - 1 <= 4 and ranks below 2^32, from the 32-bit table (the per-item path).
+__device__ __forceinline__ void tp_tri_unrank32(int mA, int p, int jt, unsigned rank, u64 &a0, u64 &a1) {
+    unsigned lo32 = 0, hi32 = 0;
+    int cnt = 0, hi = mA;
+    for (int i = p - 1; i >= 1; --i) {
+        const uint32_t *row = tp_tri_c32[i - 1];
+        int lo; // the largest one with C(lo,i) <= rank (it is below hi)
+        if (i <= 3) { // closed-form estimate, then a step or two along the table
+            lo = i == 1 ? (int)rank
+                        : i == 2 ? (int)((1.0f + sqrtf(1.0f + 8.0f * (float)rank)) * 0.5f) : (int)cbrtf(6.0f * (float)rank) + 1;
+            lo = min(max(lo, i - 1), hi - 1);
+            while (row[lo] > rank) lo--;
+            while (lo + 1 < hi && row[lo + 1] <= rank) lo++;
+        } else {
+            lo = i - 1;
+            int h = hi; // C(lo,i) <= rank < C(h,i)
+            while (h - lo > 1) {
+                const int mid = (lo + h) >> 1;
+                if (row[mid] <= rank) lo = mid;
+                else h = mid;
+            }
+        }
+        rank -= row[lo];
+        hi = lo;
+        const unsigned pos = (unsigned)(jt + 1 + lo);
+        if (cnt < 4) lo32 |= pos << (8 * cnt);
+        else hi32 |= pos << (8 * (cnt - 4));
+        cnt++;
+    }
+    if (cnt < 4) lo32 |= (unsigned)jt << (8 * cnt);
+    else hi32 |= (unsigned)jt << (8 * (cnt - 4));
+    a0 = ((u64)hi32 << 32) | lo32;
+    a1 = 0;
+}
+
+// Offsets inside a warp's area: T vectors of the DW walk levels, then T' and T'' of the prefix pair ([DW+2][M]),
+// [M/8][32] lane vectors (16 bytes each), byte area.
+#define TP_TRI_VA_OFF(M, DW) ((unsigned)((DW) + 2) * (M) * 2u)
+#define TP_TRI_WB_OFF(M, DW) (TP_TRI_VA_OFF(M, DW) + (unsigned)((M) / 8) * 512u)
+
+// The exact re-walk of one leaf for this lane and one prefix of the pair (half 0: last walked position as stored,
+// T'; half 1: one below, T''): candidates, and leaves without a table.  Everything it needs is read back from
+// shared memory, the lane's A is unranked again.
 template <int M, int DW>
-__device__ __noinline__ void tp_tri_slow(int b_leaf, int base, TpKey *best) {
+__device__ __noinline__ void tp_tri_slow(int b_leaf, int base, int half, TpKey *best) {
     const TpTriBlock &blk = tp_tri_blk;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned char *wb = blk.warp0 + (size_t)warp * blk.per_warp;
+    const uint8_t *area = wb + TP_TRI_WB_OFF(M, DW);
+    uint8_t walked[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) walked[i] = area[i];
+    walked[DW - 1] = (uint8_t)(walked[DW - 1] - half);
     TpSplitWarp w;
-    w.tstack = (uint16_t *)wb;
-    w.va = (uint32_t *)(wb + (size_t)(DW + 1) * M * 2);
-    w.bstack = (uint8_t *)(w.va + (M / 8) * 32 * 4);
+    w.tstack = (uint16_t *)wb + half * M; // level DW of this view: T' or T''
+    w.va = (uint32_t *)(wb + TP_TRI_VA_OFF(M, DW));
+    w.bstack = walked;
     w.lane = lane;
-    const int jt = w.bstack[TP_TRI_WB_JT];
-    const unsigned ac = *(const unsigned *)(w.bstack + TP_TRI_WB_AC);
+    const int jt = area[TP_TRI_WB_JT];
+    const unsigned ac = *(const unsigned *)(area + TP_TRI_WB_AC);
     const int kcols = blk.sh.k + 1;
     const u64 *binom = blk.s.binom;
     auto C = [&](int a, int b) -> u64 { return (b < 0 || a < b) ? 0ull : binom[a * kcols + b]; };
@@ -331,11 +350,6 @@ __device__ __noinline__ void tp_tri_slow(int b_leaf, int base, TpKey *best) {
     tp_tri_unrank(C, mA, blk.sh.p, jt, rank, w.a0, w.a1);
     tp_split_slow<M>(blk.sh, blk.s, w, DW + 1, b_leaf, b_leaf, base, &tp_tri_bound, *best);
 }
-
-// Offsets inside a warp's area: [DW+1][M] T vectors, [M/8][32] lane vectors (16 bytes each), byte area.
-#define TP_TRI_VA_OFF(M, DW) ((unsigned)((DW) + 1) * (M) * 2u)
-#define TP_TRI_WB_OFF(M, DW) (TP_TRI_VA_OFF(M, DW) + (unsigned)((M) / 8) * 512u)
-
 
 struct TpTriHot { // what the walk keeps in registers: 32-bit shared addresses and a few numbers
     unsigned wb;  // the warp's area
@@ -368,43 +382,43 @@ __device__ __forceinline__ unsigned tp_lds8v(unsigned addr) {
     return v;
 }
 
-// Row pairs H..0 of a pass, straight-line.
-template <int H>
+// Leaves up to TP_TRI_LT are straight-line code with compile-time positions (their tables sit at
+// constant offsets, their own VT terms are registers): an average leaf holds only ~60-100 pairs, so
+// for the small leaves the work AROUND the rows (dispatch, table lookup, the lane's own terms, loop)
+// would otherwise weigh as much as the rows.  The leaves below TP_TRI_LB form one basic block with a
+// single test at its end, so that their table loads can all be issued ahead.
+// (More straight-line leaves cost instruction-cache reach.)
+#ifndef TP_TRI_LT
+#define TP_TRI_LT 14
+#endif
+#ifndef TP_TRI_LB
+#define TP_TRI_LB 8
+#endif
+
+// Rows JX .. 1 of the leaf at tl, odd rows on chain A and even rows on chain B.
+template <int JX>
 struct TpTriRows {
-    static __device__ __forceinline__ void run(const unsigned (&VT)[TP_TRI_NREG], unsigned tA, unsigned tB,
-                                               unsigned &runA, unsigned &runB, unsigned one) {
-        tp_tri_rowpair<H>(VT, tA, tB, runA, runB, one);
-        if constexpr (H > 0) TpTriRows<H - 1>::run(VT, tA, tB, runA, runB, one);
+    static __device__ __forceinline__ void run(const unsigned (&VT)[TP_TRI_NREG], unsigned tl, unsigned &runA,
+                                               unsigned &runB) {
+        if constexpr (JX >= 1) {
+            tp_tri_row<JX>(VT, tl, (JX & 1) ? runA : runB);
+            TpTriRows<JX - 1>::run(VT, tl, runA, runB);
+        }
     }
 };
 
-// Leaf pairs below TP_TRI_GT are straight-line code with compile-time positions (their tables sit
-// at constant offsets, their own VT terms are registers): an average leaf holds only ~60-100
-// pairs, so for the small passes the work AROUND the rows (dispatch, table lookup, the lane's own
-// terms, loop) would otherwise weigh as much as the rows.  The passes below TP_TRI_GB form one
-// basic block with a single test at its end, so that their table loads can all be issued ahead.
-// (More straight-line passes cost instruction-cache reach: 12 passes are ~27 KB of code.)
-#ifndef TP_TRI_GT
-#define TP_TRI_GT 8
-#endif
-#ifndef TP_TRI_GB
-#define TP_TRI_GB 4
-#endif
-
-// A compile-time pass: leaves 2G+2 (A) and 2G+1 (B), folded into the running minimum xm; passes at
-// or above TP_TRI_GB, and pass 0, end with the test of what has accumulated.
-#define TP_TRI_PASS(G)                                                                                  \
-    case G:                                                                                             \
-        if constexpr ((G) < TP_TRI_GT) {                                                                \
-            constexpr unsigned OFFB = (unsigned)tp_tri_pair_base(G) * 16u;                              \
-            constexpr unsigned OFFA = OFFB + (unsigned)tp_tri_off((G) + 1) * 16u;                       \
+// A straight-line leaf B, folded into the running minimum xm; leaves at or above TP_TRI_LB, and leaf 2,
+// end with the test of what has accumulated.
+#define TP_TRI_PASS(B)                                                                                  \
+    case B:                                                                                             \
+        if constexpr ((B) <= TP_TRI_LT) {                                                               \
             unsigned runA = TP_BIG2 + TP_BIG2, runB = TP_BIG2 + TP_BIG2;                                \
-            TpTriRows<(G)>::run(VT, tbl + OFFA, tbl + OFFB, runA, runB, one);                           \
-            xm = __vimin3_u16x2(xm, runA + VT[2 * (G) + 2], runB + VT[2 * (G) + 1]);                    \
-            if constexpr ((G) >= TP_TRI_GB || (G) == 0) {                                               \
+            TpTriRows<(B) - 1>::run(VT, tbl + (unsigned)tp_tri_leaf_off(B) * 4u, runA, runB);           \
+            xm = __vimin3_u16x2(xm, runA + VT[(B)], runB + VT[(B)]);                                    \
+            if constexpr ((B) >= TP_TRI_LB || (B) == 2) {                                               \
                 if (__vminu2(xm, room2) != room2) {                                                     \
-                    g_to = (G);                                                                         \
-                    g = min(g, (G) >= TP_TRI_GB ? (G) : TP_TRI_GB - 1);                                 \
+                    b_to = (B);                                                                         \
+                    b = min(b, (B) >= TP_TRI_LB ? (B) : TP_TRI_LB - 1);                                 \
                     goto rare;                                                                          \
                 }                                                                                       \
                 xm = 0xFFFFFFFFu;                                                                       \
@@ -412,30 +426,36 @@ struct TpTriRows {
         }                                                                                               \
         [[fallthrough]];
 
-// All leaves b in [lo, hi) of one walked prefix.  va, tl, tbl: shared addresses of the lane's vectors
-// (chunk c at va + 512 c), of the prefix's T vector and of the S3 table; base: the score of
-// everything above the triple (c_req, inside A, A x walked, inside walked, unary terms); gcap_active:
-// table cap, negated for a lane without a real A.  Inlined into the kernel itself (only an entry
-// function may use all 128 registers; everything cold around it is a call).
+// All leaves b in [lo_leaf, hi_leaf) of a pair of walked prefixes, hi the walked value of the first one (leaves are
+// below it; the second prefix is without leaf hi - 1); the range is all of [2, hi) except in an item that holds one
+// walked value cut by its leaves.  va, t1, tbl:
+// shared addresses of the lane's vectors (chunk c at va + 512 c), of the pair's T vectors (T' at t1, T'' 2 M bytes
+// on) and of the S3 table; base0, base1: the score of everything above the triple (c_req, inside A, A x walked,
+// inside walked, unary terms) for the two prefixes, base1 < 0 when there is no second prefix; gcap_active: table
+// cap, negated for a lane without a real A.  Inlined into the kernel itself (only an entry function may use all
+// 128 registers; everything cold around it is a call).
 template <int M, int DW>
-__device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned tl, unsigned tbl, int gcap_active, int hi, int lo,
-                                              int base, TpKey *best) {
-    // The lane registers: positions below hi (at most the 64 that have registers); the rest is never
+__device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned t1, unsigned tbl, int gcap_active, int hi, int hi_leaf,
+                                              int lo_leaf, int base0, int base1, TpKey *best) {
+    // The lane registers: positions below hi (at most the 48 that have registers); the rest is never
     // read.  They are rebuilt after every call of the slow path rather than kept alive across it.
     unsigned VT[TP_TRI_NREG];
-    const int vt_chunks = min((hi + 7) >> 3, TP_TRI_NREG / 8);
-    const int gcap = abs(gcap_active);
-    auto vt_at = [&](int j) -> int { // (V + T)[j] of this lane: two 16-bit loads
-        return (int)tp_lds16(va + (unsigned)((j >> 3) * 512 + (j & 7) * 2)) + (int)tp_lds16(tl + 2u * (unsigned)j);
+    const int vt_chunks = min((hi_leaf + 7) >> 3, TP_TRI_NREG / 8);
+    const int lmax = 2 * abs(gcap_active);
+    auto vt2_at = [&](int j) -> unsigned { // (V + T')[j] | (V + T'')[j] << 16 of this lane: three 16-bit loads
+        const unsigned v = tp_lds16(va + (unsigned)((j >> 3) * 512 + (j & 7) * 2));
+        return (v + tp_lds16(t1 + 2u * (unsigned)j)) | ((v + tp_lds16(t1 + 2u * M + 2u * (unsigned)j)) << 16);
     };
-    const unsigned one = (unsigned)(*(volatile int *)&tp_tri_blk.gcap >> 30) + 1u; // 1, but not to the compiler
-    const int room = *(volatile int *)&tp_tri_bound - base + 1; // a total below this is a candidate
-    // (a lane without a real A never reports: its threshold is 0)
-    const unsigned room2 = gcap_active > 0 ? (unsigned)min(max(room, 0), 0xFFFF) * 0x10001u : 0u;
-    int g = (hi - 2) >> 1; // leaves 2g+2 (A; may be hi, not a leaf of this range) and 2g+1 (B; may be lo - 1)
-    int g_to = 0;          // on the way to `rare`: passes g .. g_to reported
-    unsigned xA = 0, xB = 0;
-    for (;;) { // (re-entered after a call of the slow path)
+    // a total below its half of room2 is a candidate (real totals stay below TP_BIG, switched-off ones do not);
+    // a lane without a real A, and the missing second prefix, never report: threshold 0
+    const int bound = *(volatile int *)&tp_tri_bound;
+    const unsigned room_lo = (unsigned)min(max(bound - base0 + 1, 0), (int)TP_BIG - 1);
+    const unsigned room_hi = base1 >= 0 ? (unsigned)min(max(bound - base1 + 1, 0), (int)TP_BIG - 1) : 0u;
+    const unsigned room2 = gcap_active > 0 ? (room_lo | (room_hi << 16)) : 0u;
+    int b = hi_leaf - 1; // the next leaf
+    int b_to = 2;   // on the way to `rare`: leaves b .. b_to reported
+    unsigned x = 0; // what they reported (0: all of them, both prefixes)
+    for (;;) {      // (re-entered after a call of the slow path)
         switch (vt_chunks) {
 #if TP_TRI_GC > 24
             TP_TRI_VT_CASE(7) TP_TRI_VT_CASE(6)
@@ -443,80 +463,104 @@ __device__ __forceinline__ void tp_tri_leaves(unsigned va, unsigned tl, unsigned
             TP_TRI_VT_CASE(5) TP_TRI_VT_CASE(4) TP_TRI_VT_CASE(3) TP_TRI_VT_CASE(2) TP_TRI_VT_CASE(1) TP_TRI_VT_CASE(0)
         default: break;
         }
-        // ---- the generic pass: big leaves, ranges that do not reach down to leaf 2, and a first
-        // pass whose leaf A is not part of the range ----------------------------------------------
-        for (; 2 * g + 2 >= lo && (g >= TP_TRI_GT || lo > 2 || 2 * g + 2 >= hi); --g) {
-            const int bA = 2 * g + 2, bB = 2 * g + 1;
-            g_to = g;
-            if (g >= gcap) { // no table up here: the exact re-walk prunes rows against the bound
-                xA = xB = 0u;
+        // ---- the generic pass: one leaf above TP_TRI_LT, rows in pairs through a switch ----------
+        for (; b > TP_TRI_LT && b >= lo_leaf; --b) {
+            b_to = b;
+            if (b > lmax) { // no table up here: the exact re-walk prunes rows against the bound
+                x = 0u;
                 goto rare;
             }
-            const uint4 pi = tp_tri_pair_info[g];
-            const unsigned tB = tbl + pi.x, tA = tB + pi.y;
+            const uint4 li = tp_tri_leaf_info[b];
+            const unsigned tl = tbl + li.x;
             unsigned runA = TP_BIG2 + TP_BIG2, runB = TP_BIG2 + TP_BIG2;
-#if TP_TRI_PREFETCH
-            const unsigned off_g = pi.z;
-            uint4 bufA[2], bufB[2]; // (the entry chunk goes to both sets: which one row pair g reads is a compile-time fact)
-            bufA[0] = bufA[1] = tp_lds128v(tA + off_g);
-            bufB[0] = bufB[1] = tp_lds128v(tB + off_g);
-#endif
-            switch (g) {
+            uint4 bufA[2], bufB[2]; // (the entry chunks go to both buffers: which one the top pair reads is a compile-time fact)
+            bufA[0] = bufA[1] = tp_lds128v(tl + li.y);
+            bufB[0] = bufB[1] = tp_lds128v(tl + li.z);
+            switch ((b - 1) >> 1) {
 #if TP_TRI_GC > 24
                 TP_TRI_CASE8(24)
 #endif
                 TP_TRI_CASE8(16) TP_TRI_CASE8(8) TP_TRI_CASE8(0)
             default: break;
             }
-            // the leaves' own terms (bA == hi is not a leaf, and can be one past the lane vector)
-            const int vbA = vt_at(min(bA, hi - 1)), vbB = vt_at(bB);
-            xA = bA < hi ? runA + (unsigned)vbA * 0x10001u : 0xFFFFFFFFu;
-            xB = bB >= lo ? runB + (unsigned)vbB * 0x10001u : 0xFFFFFFFFu;
-            if (__vminu2(__vminu2(xA, xB), room2) != room2) goto rare;
+            x = __vminu2(runA, runB) + vt2_at(b);
+            if (__vminu2(x, room2) != room2) goto rare;
         }
-        if (2 * g + 2 < lo) return;
-        { // ---- leaves 2g+2 .. 2 in one straight line (all of them leaves of the range) -----------
+        if (b < lo_leaf) return;
+        { // ---- leaves b .. 2 in one straight line (a range that starts among them rescans the few below it) ----
             unsigned xm = 0xFFFFFFFFu;
-            xA = xB = 0u; // should a block report, every leaf of it is re-walked
-            switch (g) {
-                TP_TRI_PASS(15) TP_TRI_PASS(14) TP_TRI_PASS(13) TP_TRI_PASS(12)
+            x = 0u; // should a block report, every leaf of it is re-walked
+            switch (b) {
+                TP_TRI_PASS(16) TP_TRI_PASS(15) TP_TRI_PASS(14) TP_TRI_PASS(13) TP_TRI_PASS(12)
                 TP_TRI_PASS(11) TP_TRI_PASS(10) TP_TRI_PASS(9) TP_TRI_PASS(8) TP_TRI_PASS(7) TP_TRI_PASS(6)
-                TP_TRI_PASS(5) TP_TRI_PASS(4) TP_TRI_PASS(3) TP_TRI_PASS(2) TP_TRI_PASS(1) TP_TRI_PASS(0)
+                TP_TRI_PASS(5) TP_TRI_PASS(4) TP_TRI_PASS(3) TP_TRI_PASS(2)
             default: break;
             }
             return;
         }
-    rare: // passes g .. g_to reported (or have no table): re-walk their leaves exactly, then go on below
-        for (; g >= g_to; --g) {
-            if (__vminu2(xA, room2) != room2 && 2 * g + 2 < hi && 2 * g + 2 >= lo)
-                tp_tri_slow<M, DW>(2 * g + 2, base + vt_at(2 * g + 2), best);
-            if (__vminu2(xB, room2) != room2 && 2 * g + 1 >= lo)
-                tp_tri_slow<M, DW>(2 * g + 1, base + vt_at(2 * g + 1), best);
+    rare: // leaves b .. b_to reported (or have no table): re-walk them exactly, then go on below
+        for (; b >= b_to; --b) {
+            const unsigned vtb = vt2_at(b);
+            if (min(x & 0xFFFFu, room2 & 0xFFFFu) != (room2 & 0xFFFFu))
+                tp_tri_slow<M, DW>(b, base0 + (int)(vtb & 0xFFFFu), 0, best);
+            if (min(x >> 16, room2 >> 16) != (room2 >> 16) && b < hi - 1)
+                tp_tri_slow<M, DW>(b, base1 + (int)(vtb >> 16), 1, best);
         }
-        if (2 * g + 2 < lo) return;
+        if (b < lo_leaf) return;
     }
 }
 
-// The warp-uniform walk over the DW positions above the triple; level L picks b in [lo, hi).
+// The warp-uniform walk over the DW positions above the triple; level L picks b in [lo, hi).  The last
+// level takes its values two at a time.
 template <int M, int DW, int L>
 struct TpTriWalk {
     static __device__ __forceinline__ void run(const TpTriHot &w, int hi, int lo, int lb, int sb, TpKey *best) {
+        static_assert(DW >= 1 && L < DW, "the pair of prefixes is made at the last walked level");
         const unsigned tl = w.wb + (unsigned)(L * M * 2);              // T_L
         const unsigned va = w.wb + TP_TRI_VA_OFF(M, DW) + 16u * w.lane; // this lane's V, chunk c at + 512 c
-        if constexpr (L == DW) {
-            if (hi > lo) tp_tri_leaves<M, DW>(va, tl, w.tbl, w.gcap_active, hi, lo, lb + sb, best);
-        } else {
-            const unsigned bst = w.wb + TP_TRI_WB_OFF(M, DW);
-            for (int b = hi - 1; b >= lo; --b) {
-                const unsigned pk = tp_lds32v(va + (unsigned)((b >> 3) * 512 + ((b >> 1) & 3) * 4));
-                const int lb2 = lb + (int)((b & 1) ? (pk >> 16) : (pk & 0xFFFF));
-                const int sb2 = sb + (int)tp_lds16v(tl + 2u * b);
-                // T_{L+1} = T_L + W[b] on the positions below b (the rest is never read)
-                const unsigned dst = tl + M * 2, rw = w.wp + (unsigned)(b * w.rsp) * 2u;
-                __syncwarp(); // lanes still in the slow path of an earlier leaf read T_{L+1} and the byte area
+        const unsigned bst = w.wb + TP_TRI_WB_OFF(M, DW);
+        auto v_at = [&](int j) -> int { // V[j] of this lane
+            const unsigned pk = tp_lds32v(va + (unsigned)((j >> 3) * 512 + ((j >> 1) & 3) * 4));
+            return (int)((j & 1) ? (pk >> 16) : (pk & 0xFFFFu));
+        };
+        if constexpr (L == DW - 1) {
+            const unsigned t1 = w.wb + (unsigned)(DW * M * 2); // T', and T'' after it
+            // an item that holds a single first walked value may be cut by the position below it: here, the leaves
+            const int lo_leaf = L == 0 ? max(2, (int)tp_lds8v(bst + 8)) : 2;
+            const int cap_leaf = L == 0 ? (int)tp_lds8v(bst + 9) : TP_MAX_N;
+            for (int b = hi - 1; b >= lo; b -= 2) {
+                const int b1 = b - 1; // (a position even when it is below lo: lo >= 3)
+                const int base0 = lb + v_at(b) + sb + (int)tp_lds16v(tl + 2u * b);
+                const int base1 = b1 >= lo ? lb + v_at(b1) + sb + (int)tp_lds16v(tl + 2u * b1) : -1;
+                // T' = T_L + W[b], T'' = T_L + W[b - 1] on the positions below (the rest is never read), with
+                // T''[b - 1] = TP_BIG: leaf b - 1 belongs to the first prefix only
+                const unsigned rw0 = w.wp + (unsigned)(b * w.rsp) * 2u, rw1 = w.wp + (unsigned)(b1 * w.rsp) * 2u;
+                __syncwarp(); // lanes still in the slow path of an earlier leaf read T', T'' and the byte area
                 if (w.lane == 0) tp_sts8(bst + L, (unsigned)b);
                 // (the same trip count for every lane: a lane-dependent one leaves the warp split in two
                 // groups that would each run the whole leaf stage below on their own)
+#pragma unroll
+                for (int w0 = 0; w0 < M / 2; w0 += 32) {
+                    const int wd = w0 + w.lane;
+                    if (wd < M / 2) {
+                        const unsigned t = tp_lds32v(tl + 4u * wd);
+                        tp_sts32(t1 + 4u * wd, t + tp_lds32v(rw0 + 4u * wd));
+                        unsigned u = t + tp_lds32v(rw1 + 4u * wd);
+                        if (wd == (b1 >> 1)) u = (b1 & 1) ? ((u & 0xFFFFu) | (TP_BIG << 16)) : ((u & 0xFFFF0000u) | TP_BIG);
+                        tp_sts32(t1 + 2u * M + 4u * wd, u);
+                    }
+                }
+                __syncwarp();
+                tp_tri_leaves<M, DW>(va, t1, w.tbl, w.gcap_active, b, min(b, cap_leaf), lo_leaf, base0, base1, best);
+            }
+        } else {
+            for (int b = hi - 1; b >= lo; --b) {
+                const int lb2 = lb + v_at(b);
+                const int sb2 = sb + (int)tp_lds16v(tl + 2u * b);
+                // T_{L+1} = T_L + W[b] on the positions below b (the rest is never read)
+                const unsigned dst = tl + M * 2, rw = w.wp + (unsigned)(b * w.rsp) * 2u;
+                __syncwarp(); // lanes still in the slow path of an earlier leaf read the T vectors and the byte area
+                if (w.lane == 0) tp_sts8(bst + L, (unsigned)b);
 #pragma unroll
                 for (int w0 = 0; w0 < M / 2; w0 += 32) {
                     const int wd = w0 + w.lane;
@@ -534,45 +578,69 @@ struct TpTriWalk {
     }
 };
 
-// Build the S3 table of this request from the plain table wp (reversed positions), one leaf per
-// warp at a time, one 16-byte chunk per lane.  hmap[c] = row pair of chunk c (the same for every leaf).
-static __device__ void tp_tri_build_table(uint4 *tbl, const uint16_t *pair_base, const uint8_t *hmap, int gcap,
-                                          const uint16_t *wp, int rsp) {
+// Build the S3 table of this request from the plain table wp (reversed positions): a warp per leaf, a word per
+// lane and turn.  rowmap[w] = the row of word w inside a leaf (the same for every leaf).
+static __device__ void tp_tri_build_table(uint32_t *tbl, const uint8_t *rowmap, int gcap, const uint16_t *wp, int rsp) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    // every turn of a warp takes one leaf from the light end of the list and one from the heavy end
-    auto fill = [&](int lf) { // leaf lf + 1: 2g+1 first, then 2g+2
-        const int g = lf >> 1, b = lf + 1;
-        const int nchunks = tp_tri_off(g + 1);
-        uint4 *dst = tbl + pair_base[g] + ((lf & 1) ? nchunks : 0);
+    auto fill = [&](int b) {
+        uint32_t *dst = tbl + (tp_tri_leaf_info[b].x >> 2);
+        const int real = tp_tri_c2(b), words = tp_tri_leaf_words(b);
         const uint16_t *rb = wp + b * rsp;
-        for (int c = lane; c < nchunks; c += 32) {
-            const int h = hmap[c], e0 = (c - tp_tri_off(h)) * 4;
-            const int r0 = 2 * h, r1 = 2 * h + 1;
-            const bool has1 = r1 < b;
-            const uint16_t *w0 = wp + r0 * rsp, *w1 = wp + r1 * rsp;
-            const unsigned c0 = rb[r0], c1 = has1 ? rb[r1] : 0;
-            unsigned out[4];
-#pragma unroll
-            for (int i = 0; i < 4; i++) {
-                const int e = e0 + i;
-                const unsigned be = rb[e];
-                const unsigned lo = e < r0 ? w0[e] + be + c0 : TP_BIG;
-                const unsigned hi = (has1 && e < r1) ? w1[e] + be + c1 : TP_BIG;
-                out[i] = lo | (hi << 16);
+        for (int w = lane; w < words; w += 32) {
+            unsigned v = TP_BIG;
+            if (w < real) {
+                const int jx = rowmap[w], jy = w - tp_tri_c2(jx);
+                v = (unsigned)rb[jx] + rb[jy] + wp[jx * rsp + jy];
             }
-            dst[c] = make_uint4(out[0], out[1], out[2], out[3]);
+            dst[w] = v * 0x10001u;
         }
     };
-    for (int i = warp; i < gcap; i += nw) {
-        fill(i);
-        fill(2 * gcap - 1 - i);
+    // every turn of a warp takes one leaf from the light end of the list and one from the heavy end
+    const int top = 2 * gcap, n_leaves = top - 1; // leaves 2 .. top
+    for (int i = warp; 2 * i < n_leaves; i += nw) {
+        fill(2 + i);
+        if (2 + i != top - i) fill(top - i);
     }
 }
 
-// Per-warp shared memory: T vectors of the DW + 1 levels, the lane vectors, the byte area.
+// Per-warp shared memory: T vectors (DW walk levels + the pair), the lane vectors, the byte area.
 template <int M, int DW>
 static __host__ __device__ inline size_t tp_tri_per_warp() {
-    return (size_t)(DW + 1) * M * 2 + (size_t)(M / 8) * 32 * 16 + TP_TRI_WB_BYTES;
+    return (size_t)(DW + 2) * M * 2 + (size_t)(M / 8) * 32 * 16 + TP_TRI_WB_BYTES;
+}
+
+// The lane vector V (positions below 8 nch) and the score inside A for a lane set of P <= 4 positions (one per
+// byte of a32), by 32-bit shared addresses: the per-item path of every search up to k' = 10.
+template <int P>
+__device__ __forceinline__ int tp_tri_lane_vector(unsigned a32, unsigned wp_s, unsigned t0_s, unsigned va_lane, int rsp,
+                                                  int nch, int c_req) {
+    unsigned row[P], pos[P];
+#pragma unroll
+    for (int i = 0; i < P; i++) {
+        pos[i] = (a32 >> (8 * i)) & 0xFFu;
+        row[i] = wp_s + pos[i] * (unsigned)rsp * 2u;
+    }
+    for (int c = 0; c < nch; c++) {
+        uint4 v = tp_lds128(row[0] + 16u * c);
+#pragma unroll
+        for (int i = 1; i < P; i++) {
+            const uint4 r = tp_lds128(row[i] + 16u * c);
+            v.x += r.x;
+            v.y += r.y;
+            v.z += r.z;
+            v.w += r.w;
+        }
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(va_lane + 512u * c), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+                     : "memory");
+    }
+    int sA = c_req;
+#pragma unroll
+    for (int i = 0; i < P; i++) {
+        sA += (int)tp_lds16(t0_s + 2u * pos[i]);
+#pragma unroll
+        for (int i2 = 0; i2 < i; i2++) sA += (int)tp_lds16(row[i] + 2u * pos[i2]);
+    }
+    return sA;
 }
 
 // Set-up of one work item (pivot, chunk of 32 lane sets, slice) for the calling warp: the lane's A,
@@ -588,11 +656,14 @@ __device__ __noinline__ bool tp_tri_item_setup(unsigned item, TpTriItem *out) {
     const int n = blk.sh.n, p = blk.sh.p, q = blk.sh.q, rsp = blk.sh.rsp;
     const uint16_t *wp = blk.sh.wp, *t0 = blk.t0;
     unsigned char *wb = blk.warp0 + (size_t)warp * blk.per_warp;
-    uint32_t *va = (uint32_t *)(wb + (size_t)(DW + 1) * M * 2); // [M/8][32][4]
+    uint32_t *va = (uint32_t *)(wb + TP_TRI_VA_OFF(M, DW));     // [M/8][32][4]
     uint8_t *bstack = (uint8_t *)(va + (M / 8) * 32 * 4);       // TP_TRI_WB_BYTES
     const int kcols = blk.sh.k + 1;
     const u64 *binom = blk.s.binom;
     auto C = [&](int a, int b) -> u64 { return (b < 0 || a < b) ? 0ull : binom[a * kcols + b]; };
+    // the grid-wide bound word: read now, looked at after the slice arithmetic (a global load's latency apart)
+    unsigned theirs_inv = 0;
+    if (lane == 0 && blk.g_bound_inv) asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(theirs_inv) : "l"(blk.g_bound_inv));
     // ---- item -> (pivot, chunk of A's, slice of the first position below the lane set) ----
     int e = 0;
     const int n_entries = blk.n_entries;
@@ -610,19 +681,43 @@ __device__ __noinline__ bool tp_tri_item_setup(unsigned item, TpTriItem *out) {
     TpSlice sl{q - 1, jt, 0, TP_MAX_N, false};
     {
         auto cum = [&](int b) -> int { return tp_tri_cum[b]; };
-        if (!tp_split_slice(C, cum, jt, q, (int)tp_tri_pieces[e], blk.b_star, (int)slice, sl)) return false; // empty
+        const int np = (int)tp_tri_pieces[e];
+        if (tp_tri_cuts_ok && (int)slice < np) { // the boundaries are in the tables
+            const int cb = tp_tri_cut_base[e] + (int)slice;
+            sl.b0_lo = tp_tri_cuts[cb];
+            sl.b0_hi = tp_tri_cuts[cb + 1];
+            if (sl.b0_lo >= sl.b0_hi) return false; // empty
+        } else if (tp_tri_cuts_ok && q == 4) { // a pair (b, b - 1) of single values, cut by the leaves (tp_split_slice)
+            const int b_eff = tp_split_bstar(jt, blk.b_star, true), t = (int)slice - np;
+            int lo = 0, hi = (jt - b_eff) >> 1;
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if ((int)tp_tri_cum[b_eff + 1 + 2 * mid] <= t) lo = mid;
+                else hi = mid;
+            }
+            const int b = b_eff + 1 + 2 * lo;
+            const int nsub = (int)tp_tri_cum[b + 2] - (int)tp_tri_cum[b], sub = t - (int)tp_tri_cum[b];
+            sl.b0_lo = b - 1;
+            sl.b0_hi = b + 1;
+            if (nsub > 1) {
+                sl.b1_lo = tp_tri_lcuts[b][sub];
+                sl.b1_hi = tp_tri_lcuts[b][sub + 1];
+                sl.cut_again = true;
+                if (sl.b1_lo >= sl.b1_hi) return false;
+            }
+        } else if (!tp_split_slice(C, cum, jt, q, np, blk.b_star, (int)slice, sl, true)) {
+            return false; // empty
+        }
     }
     __syncwarp(); // the previous item's slow-path lanes are done with the warp's areas
     if (lane == 0 && blk.g_bound_inv) { // what other blocks found so far, and what this one did
-        const int theirs = (int)(0x7FFFFFFFu - *(volatile unsigned *)blk.g_bound_inv);
+        const int theirs = (int)(0x7FFFFFFFu - theirs_inv);
         const int ours = *(volatile int *)&tp_tri_bound;
         if (theirs < ours) atomicMin(&tp_tri_bound, theirs);
         else if (ours < theirs) atomicMax(blk.g_bound_inv, 0x7FFFFFFFu - (unsigned)ours);
     }
     {
-        u64 per_lane; // sets below the lane set that this item scores per lane
-        if (sl.cut_again) per_lane = C(sl.b1_hi, q - 1) - C(sl.b1_lo, q - 1);
-        else per_lane = C(sl.b0_hi, q) - C(sl.b0_lo, q);
+        const u64 per_lane = tp_split_slice_count(C, sl, q); // sets below the lane set that this item scores per lane
         if (lane == 0) {
             const u64 na = C(n - 1 - jt, p - 1);
             *(u64 *)(bstack + TP_TRI_WB_COUNT) += per_lane * (u64)min((u64)32, na - (u64)ac * 32);
@@ -639,18 +734,26 @@ __device__ __noinline__ bool tp_tri_item_setup(unsigned item, TpTriItem *out) {
     const int active = rank < NA;
     if (!active) rank = NA - 1;
     u64 a0, a1;
-    tp_tri_unrank(C, mA, p, jt, rank, a0, a1);
+    if (p <= 5 && NA < 0xFFFFFFFFull) tp_tri_unrank32(mA, p, jt, (unsigned)rank, a0, a1);
+    else tp_tri_unrank(C, mA, p, jt, rank, a0, a1);
     auto elem = [&](int i) { return (int)(((i < 8 ? a0 : a1) >> (8 * (i & 7))) & 0xFF); };
     // ---- V = sum of the A rows (positions < jt) -> shared memory; sA = score inside A ----
     int sA = blk.c_req;
-    {
+    const int nch = (min(jt, sl.b0_hi) + 7) >> 3; // (nothing at or above the slice's top is ever read)
+    if (p >= 2 && p <= 4) {
+        const unsigned wp_s = (unsigned)__cvta_generic_to_shared(wp), t0_s = (unsigned)__cvta_generic_to_shared(t0);
+        const unsigned va_lane = (unsigned)__cvta_generic_to_shared(va) + 16u * lane;
+        const unsigned a32 = (unsigned)a0;
+        sA = p == 4 ? tp_tri_lane_vector<4>(a32, wp_s, t0_s, va_lane, rsp, nch, sA)
+                    : p == 3 ? tp_tri_lane_vector<3>(a32, wp_s, t0_s, va_lane, rsp, nch, sA)
+                             : tp_tri_lane_vector<2>(a32, wp_s, t0_s, va_lane, rsp, nch, sA);
+    } else {
         int rowoff[TP_SPLIT_MAX_P];
 #pragma unroll
         for (int i = 0; i < TP_SPLIT_MAX_P; i++) {
             if (i >= p) break;
             rowoff[i] = elem(i) * rsp;
         }
-        const int nch = (jt + 7) >> 3;
         for (int c = 0; c < nch; c++) {
             uint4 v = make_uint4(0, 0, 0, 0);
 #pragma unroll
@@ -724,14 +827,14 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
                                           const TpReq *__restrict__ rq, const TpPlan *__restrict__ plan,
                                           unsigned *g_bound_inv) {
     unsigned char *const smem = tp_split_smem;
-    __shared__ uint8_t s_hmap[tp_tri_off(TP_TRI_GC)];
+    __shared__ uint8_t s_rowmap[tp_tri_c2(TP_TRI_LMAX)]; // word of a leaf's table -> its row
     const int n = rq->n, k = rq->k, n_req = rq->n_req;
     const int gcap = plan->tri_gcap;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x, nt = blockDim.x;
     // layout: the S3 table first (+ a zero the compiler cannot see, so that its base lives in a
     // register and rows are addressed [base + constant]), then the staged request, the plain
     // table, u, and the per-warp areas
-    uint4 *tbl = (uint4 *)smem + (plan->p >> 24);
+    uint32_t *tbl = (uint32_t *)smem + (plan->p >> 24);
     size_t off = tp_tri_table_bytes(gcap);
     const TpSmem s = tp_smem_carve(smem + off, n, k);
     off += (tp_smem_bytes(n, k) + 15) & ~(size_t)15;
@@ -742,8 +845,8 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
     off += (size_t)TP_MAX_N * 2;
     const size_t per_warp = tp_tri_per_warp<M, DW>();
     unsigned char *warp_base = smem + off + (size_t)warp * per_warp;
-    uint16_t *tstack = (uint16_t *)warp_base; // [DW+1][M]
-    uint8_t *bstack = warp_base + (size_t)(DW + 1) * M * 2 + (size_t)(M / 8) * 32 * 16;
+    uint16_t *tstack = (uint16_t *)warp_base; // [DW+2][M]
+    uint8_t *bstack = warp_base + TP_TRI_WB_OFF(M, DW);
     TP_TRI_STAMP(1);
     // ---- (1) everything that is a plain copy or a formula ------------------------------------
     if (tid == 0) {
@@ -776,11 +879,36 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         tp_tri_pieces[i] = plan->n_pieces[i];
     }
     for (int i = tid; i < TP_MAX_N + 2; i += nt) tp_tri_cum[i] = plan->cum[i];
-    for (int g = tid; g <= gcap; g += nt) tp_tri_pair_start[g] = (uint16_t)tp_tri_pair_base(g);
-    for (int g = tid; g < gcap; g += nt)
-        tp_tri_pair_info[g] = make_uint4(16u * tp_tri_pair_base(g), 16u * tp_tri_off(g + 1), 16u * tp_tri_off(g), 0u);
-    for (int h = tid; h < gcap; h += nt)
-        for (int c = tp_tri_off(h); c < tp_tri_off(h + 1); c++) s_hmap[c] = (uint8_t)h;
+    for (int i = tid; i < 4 * (TP_MAX_N + 1); i += nt) {
+        const int col = i / (TP_MAX_N + 1) + 1, m = i % (TP_MAX_N + 1);
+        const u64 c = col < TP_BINOM_COLS ? binom_g[m * TP_BINOM_COLS + col] : ~0ull;
+        tp_tri_c32[col - 1][m] = c > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)c;
+    }
+    if (warp == TP_TRI_WARPS - 1) { // where every pivot entry's slice boundaries start: a running sum of n_pieces + 1
+        int run = 0;
+        for (int bs = 0; bs < plan->n_entries; bs += 32) {
+            const int idx = bs + lane;
+            const int v = idx < plan->n_entries ? (int)plan->n_pieces[idx] + 1 : 0;
+            int incl = v;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                if (lane >= d) incl += up;
+            }
+            if (idx < plan->n_entries) tp_tri_cut_base[idx] = (uint16_t)min(run + incl - v, 0xFFFF);
+            run += __shfl_sync(0xFFFFFFFFu, incl, 31);
+        }
+        if (lane == 0) {
+            tp_tri_cut_base[plan->n_entries] = (uint16_t)min(run, 0xFFFF);
+            tp_tri_cuts_ok = run <= TP_TRI_MAX_CUTS && n <= TP_TRI_MAX_HEADS;
+        }
+    }
+    for (int b = 2 + tid; b <= 2 * gcap; b += nt) {
+        const int h = (b - 1) >> 1;
+        tp_tri_leaf_info[b] = make_uint4(4u * tp_tri_leaf_off(b), 16u * tp_tri_row_c0(2 * h + 1), 16u * tp_tri_row_c0(2 * h), 0u);
+    }
+    for (int jx = 1 + tid; jx < 2 * gcap; jx += nt)
+        for (int jy = 0; jy < jx; jy++) s_rowmap[tp_tri_c2(jx) + jy] = (uint8_t)jx;
     TP_TRI_STAMP(2);
     // ---- (2) weights: canonical byte table (seeds) and 16-bit reversed table (everything else); the
     // canonical order is read from the descriptor itself, so that no barrier separates (1) and (2) ----
@@ -841,8 +969,32 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         const int sco = tp_tri_family_seed(s, rq->n_groups, k, rq->c_req, first, stride);
         if (sco != 0x7FFFFFFF) atomicMin(&tp_tri_bound, sco);
     }
+    if (tp_tri_cuts_ok) { // the slice boundaries of every pivot entry, and the leaf cuts of the pairs
+        const int kcols = k + 1, q = plan->q, n_entries = plan->n_entries, b_star = plan->b_star;
+        const u64 *binom = s.binom;
+        auto C = [&](int a, int b) -> u64 { return (b < 0 || a < b) ? 0ull : binom[a * kcols + b]; };
+        const int total = tp_tri_cut_base[n_entries];
+        for (int idx = tid; idx < total; idx += nt) {
+            int lo = 0, hi = n_entries; // the entry whose range holds idx
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if ((int)tp_tri_cut_base[mid] <= idx) lo = mid;
+                else hi = mid;
+            }
+            const int jt = plan->jt_hi - lo, np = (int)tp_tri_pieces[lo];
+            const int b_eff = tp_split_bstar(jt, b_star, q == 4);
+            tp_tri_cuts[idx] = (uint8_t)tp_split_cut(C, jt < b_eff ? jt : b_eff, q, np, idx - (int)tp_tri_cut_base[lo], true);
+        }
+        if (q == 4)
+            for (int idx = tid; idx < TP_TRI_MAX_HEADS * (TP_SPLIT_MAX_SUB + 1); idx += nt) {
+                const int b = idx / (TP_SPLIT_MAX_SUB + 1), sub = idx - b * (TP_SPLIT_MAX_SUB + 1);
+                if (b <= b_star || b >= plan->jt_hi || b + 2 > TP_MAX_N + 1) continue;
+                const int nsub = (int)tp_tri_cum[b + 2] - (int)tp_tri_cum[b];
+                if (nsub > 1 && sub <= nsub) tp_tri_lcuts[b][sub] = (uint8_t)tp_split_cut(C, b, q - 1, nsub, sub);
+            }
+    }
     TP_TRI_STAMP(4);
-    tp_tri_build_table(tbl, tp_tri_pair_start, s_hmap, gcap, wp, rsp);
+    tp_tri_build_table(tbl, s_rowmap, gcap, wp, rsp);
     TP_TRI_STAMP(5);
     for (int i = lane; i < M; i += 32) tstack[i] = t0[i];
     __syncthreads();
@@ -902,10 +1054,7 @@ tp_exhaustive_tri(const uint8_t *__restrict__ W, int nd, const u64 *__restrict__
             const TpTriHot hot{wb, (unsigned)__cvta_generic_to_shared(tp_tri_blk.sh.wp),
                                (unsigned)__cvta_generic_to_shared(tp_tri_blk.tbl), tp_tri_blk.sh.rsp,
                                it.active ? tp_tri_blk.gcap : -tp_tri_blk.gcap, lane};
-            if constexpr (DW == 0) // the slice bounds the top of the triple itself
-                TpTriWalk<M, 0, 0>::run(hot, it.b0_hi, max(it.b0_lo, 2), it.sA, 0, &best);
-            else
-                TpTriWalk<M, DW, 0>::run(hot, it.b0_hi, max(it.b0_lo, DW + 2), it.sA, 0, &best);
+            TpTriWalk<M, DW, 0>::run(hot, it.b0_hi, max(it.b0_lo, DW + 2), it.sA, 0, &best);
             __syncwarp();
         }
         __syncwarp();

@@ -3,3 +3,4 @@
 
 #include "tp_tri.cuh"
 TP_DEFINE_TRI_LAUNCHER(64, 1)
+int tp_tri_gc() { return TP_TRI_GC; }
