@@ -101,7 +101,7 @@ class ClockSampler:
 def ncu_dram_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the search kernel, from the
     committed `ncu --set full` summary of this round (profiles/); None when there is none."""
-    name = {1: "r1_lex_ncu_full.txt", 2: "r1_split_final_c4_ncu_full.txt", 4: "r2_tri_final_c4_ncu_full.txt"}.get(kernel)
+    name = {1: "r1_lex_ncu_full.txt", 2: "r1_split_final_c4_ncu_full.txt", 4: "r2_pair_c4_ncu_full.txt"}.get(kernel)
     path = os.path.join(ROOT, "profiles", name) if name else None
     if not path or not os.path.exists(path):
         return None

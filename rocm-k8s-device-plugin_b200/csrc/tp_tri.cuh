@@ -58,6 +58,18 @@ __host__ __device__ constexpr int tp_tri_leaf_off(int b) {
     for (int i = 2; i < b; i++) s += tp_tri_leaf_words(i);
     return s;
 }
+// (the same sums as a table, for the kernel's set-up)
+struct TpTriLeafOffsets {
+    uint16_t words[TP_TRI_LMAX + 2];
+    constexpr TpTriLeafOffsets() : words() {
+        int s = 0;
+        for (int b = 2; b < TP_TRI_LMAX + 2; b++) {
+            words[b] = (uint16_t)s;
+            s += tp_tri_leaf_words(b);
+        }
+    }
+};
+static __constant__ TpTriLeafOffsets tp_tri_leaf_offsets = TpTriLeafOffsets();
 static __host__ __device__ inline size_t tp_tri_table_bytes(int gcap) { return (size_t)tp_tri_leaf_off(2 * gcap + 1) * 4; }
 // Row jx inside a leaf: 16-byte chunks c0 .. c1 hold its words (the first and the last one shared with its neighbours).
 __host__ __device__ constexpr int tp_tri_row_c0(int jx) { return tp_tri_c2(jx) / 4; }
@@ -578,21 +590,32 @@ struct TpTriWalk {
     }
 };
 
-// Build the S3 table of this request from the plain table wp (reversed positions): a warp per leaf, a word per
-// lane and turn.  rowmap[w] = the row of word w inside a leaf (the same for every leaf).
-static __device__ void tp_tri_build_table(uint32_t *tbl, const uint8_t *rowmap, int gcap, const uint16_t *wp, int rsp) {
+// Build the S3 table of this request from the plain table wp (reversed positions): a warp per leaf, a 16-byte
+// chunk per lane and turn.
+static __device__ void tp_tri_build_table(uint32_t *tbl, int gcap, const uint16_t *wp, int rsp) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     auto fill = [&](int b) {
-        uint32_t *dst = tbl + (tp_tri_leaf_info[b].x >> 2);
-        const int real = tp_tri_c2(b), words = tp_tri_leaf_words(b);
+        uint4 *dst = (uint4 *)(tbl + (tp_tri_leaf_info[b].x >> 2));
+        const int real = tp_tri_c2(b), chunks = tp_tri_leaf_words(b) >> 2;
         const uint16_t *rb = wp + b * rsp;
-        for (int w = lane; w < words; w += 32) {
-            unsigned v = TP_BIG;
-            if (w < real) {
-                const int jx = rowmap[w], jy = w - tp_tri_c2(jx);
-                v = (unsigned)rb[jx] + rb[jy] + wp[jx * rsp + jy];
+        for (int c = lane; c < chunks; c += 32) {
+            const int w = 4 * c;
+            int jx = (int)((1.0f + sqrtf(1.0f + 8.0f * (float)w)) * 0.5f); // the row of word w: C(jx,2) <= w < C(jx+1,2)
+            if (tp_tri_c2(jx) > w) jx--;
+            else if (tp_tri_c2(jx + 1) <= w) jx++;
+            int jy = w - tp_tri_c2(jx);
+            unsigned out[4];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                unsigned v = TP_BIG; // (after the rows: the missing top row of an odd leaf, and padding)
+                if (w + i < real) v = (unsigned)rb[jx] + rb[jy] + wp[jx * rsp + jy];
+                out[i] = v * 0x10001u;
+                if (++jy == jx) {
+                    jx++;
+                    jy = 0;
+                }
             }
-            dst[w] = v * 0x10001u;
+            dst[c] = make_uint4(out[0], out[1], out[2], out[3]);
         }
     };
     // every turn of a warp takes one leaf from the light end of the list and one from the heavy end
@@ -827,7 +850,6 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
                                           const TpReq *__restrict__ rq, const TpPlan *__restrict__ plan,
                                           unsigned *g_bound_inv) {
     unsigned char *const smem = tp_split_smem;
-    __shared__ uint8_t s_rowmap[tp_tri_c2(TP_TRI_LMAX)]; // word of a leaf's table -> its row
     const int n = rq->n, k = rq->k, n_req = rq->n_req;
     const int gcap = plan->tri_gcap;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, tid = threadIdx.x, nt = blockDim.x;
@@ -871,8 +893,16 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         s.gstart[i] = rq->gstart[i];
         s.gsize[i] = rq->gsize[i];
     }
-    for (int a = warp; a <= n; a += TP_TRI_WARPS)
-        for (int j = lane; j <= k; j += 32) s.binom[a * (k + 1) + j] = binom_g[a * TP_BINOM_COLS + j];
+    { // (two independent global loads per turn: the block waits for the slowest thread of this phase)
+        const int kc = k + 1, cells = (n + 1) * kc;
+        for (int i = tid; i < cells; i += 2 * nt) {
+            const int i2 = i + nt, a = i / kc, a2 = i2 / kc;
+            const u64 x = binom_g[a * TP_BINOM_COLS + (i - a * kc)];
+            const u64 y = i2 < cells ? binom_g[a2 * TP_BINOM_COLS + (i2 - a2 * kc)] : 0ull;
+            s.binom[i] = x;
+            if (i2 < cells) s.binom[i2] = y;
+        }
+    }
     for (int i = tid; i < plan->n_entries; i += nt) {
         tp_tri_item_base[i] = plan->item_base[i];
         tp_tri_n_chunks[i] = plan->n_chunks[i];
@@ -905,10 +935,8 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
     }
     for (int b = 2 + tid; b <= 2 * gcap; b += nt) {
         const int h = (b - 1) >> 1;
-        tp_tri_leaf_info[b] = make_uint4(4u * tp_tri_leaf_off(b), 16u * tp_tri_row_c0(2 * h + 1), 16u * tp_tri_row_c0(2 * h), 0u);
+        tp_tri_leaf_info[b] = make_uint4(4u * tp_tri_leaf_offsets.words[b], 16u * tp_tri_row_c0(2 * h + 1), 16u * tp_tri_row_c0(2 * h), 0u);
     }
-    for (int jx = 1 + tid; jx < 2 * gcap; jx += nt)
-        for (int jy = 0; jy < jx; jy++) s_rowmap[tp_tri_c2(jx) + jy] = (uint8_t)jx;
     TP_TRI_STAMP(2);
     // ---- (2) weights: canonical byte table (seeds) and 16-bit reversed table (everything else); the
     // canonical order is read from the descriptor itself, so that no barrier separates (1) and (2) ----
@@ -994,7 +1022,7 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
             }
     }
     TP_TRI_STAMP(4);
-    tp_tri_build_table(tbl, s_rowmap, gcap, wp, rsp);
+    tp_tri_build_table(tbl, gcap, wp, rsp);
     TP_TRI_STAMP(5);
     for (int i = lane; i < M; i += 32) tstack[i] = t0[i];
     __syncthreads();
