@@ -343,6 +343,11 @@ bool build_plan(const tp_policy *p, Prep &out) {
     if (q > 3) {
         const u64 lanes = (u64)p->sm_count * 2 * TP_SPLIT_THREADS;
         u64 cap1 = std::max<u64>(cap0, rq.total / (lanes * (u64)std::max(out.shards, 1) * 4));
+        // Kernel TRI on a shard: the pairs of single values (the items that end a shard, ~2 items per warp at 8
+        // shards) are cut finer than the pieces -- slowest shard of C4, cap1 = cap0 / (2/3 cap0) / (1/2 cap0):
+        // 4 shards 0.447 / 0.413 / 0.429 ms, 8 shards 0.282 / 0.280 / 0.260 ms (scripts/shard_sweep3.py).
+        if (pair_b0 && !out.batch && out.shards >= 4)
+            cap1 = std::max<u64>(out.shards >= 8 ? cap0 / 2 : cap0 * 2 / 3, rq.total / (lanes * (u64)out.shards * 4));
         if (out.batch) cap1 = std::max<u64>(cap0, rq.total / (batch_lanes * 4));
         if (p->tune_cap1) cap1 = std::max<u64>(64, p->tune_cap1); // tuning aid
         // (pairs: from a quarter of the cap on, so that the equal-work pieces below b_star are made of grains well
