@@ -256,6 +256,7 @@ static __shared__ uint16_t tp_tri_cut_base[TP_MAX_N + 1];
 static __shared__ uint8_t tp_tri_cuts[TP_TRI_MAX_CUTS];
 static __shared__ uint8_t tp_tri_lcuts[TP_TRI_MAX_HEADS][TP_SPLIT_MAX_SUB + 1];
 static __shared__ int tp_tri_cuts_ok;
+static __shared__ int tp_tri_next_leaf; // table build: the next leaf to fill (counted down from the largest)
 // C(m, i) for i = 1 .. 4, saturated: unranking a lane set of up to five positions in 32-bit arithmetic
 static __shared__ uint32_t tp_tri_c32[4][TP_MAX_N + 1];
 
@@ -618,12 +619,17 @@ static __device__ void tp_tri_build_table(uint32_t *tbl, int gcap, const uint16_
             dst[c] = make_uint4(out[0], out[1], out[2], out[3]);
         }
     };
-    // every turn of a warp takes one leaf from the light end of the list and one from the heavy end
-    const int top = 2 * gcap, n_leaves = top - 1; // leaves 2 .. top
-    for (int i = warp; 2 * i < n_leaves; i += nw) {
-        fill(2 + i);
-        if (2 + i != top - i) fill(top - i);
+    // warps take leaves off a counter, heaviest first (they arrive at different times: seeds, slice boundaries)
+    const int top = 2 * gcap;
+    for (;;) {
+        int i = 0;
+        if (lane == 0) i = atomicAdd(&tp_tri_next_leaf, 1);
+        i = __shfl_sync(0xFFFFFFFFu, i, 0);
+        if (top - i < 2) break;
+        fill(top - i);
     }
+    (void)warp;
+    (void)nw;
 }
 
 // Per-warp shared memory: T vectors (DW walk levels + the pair), the lane vectors, the byte area.
@@ -886,6 +892,7 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         tp_tri_blk.total_items = plan->total_items;
         tp_tri_blk.g_bound_inv = g_bound_inv;
         tp_tri_bound = 0x7FFFFFFF;
+        tp_tri_next_leaf = 0;
     }
     if (lane == 0) *(u64 *)(bstack + TP_TRI_WB_COUNT) = 0;
     for (int i = tid; i < n; i += nt) {
@@ -998,9 +1005,12 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
         if (sco != 0x7FFFFFFF) atomicMin(&tp_tri_bound, sco);
     }
     if (tp_tri_cuts_ok) { // the slice boundaries of every pivot entry, and the leaf cuts of the pairs
-        const int kcols = k + 1, q = plan->q, n_entries = plan->n_entries, b_star = plan->b_star;
+        const int kcols = k + 1, q = tp_tri_blk.sh.q, n_entries = tp_tri_blk.n_entries, b_star = tp_tri_blk.b_star;
+        const int jt_hi = tp_tri_blk.jt_hi;
         const u64 *binom = s.binom;
-        auto C = [&](int a, int b) -> u64 { return (b < 0 || a < b) ? 0ull : binom[a * kcols + b]; };
+        auto C64 = [&](int a, int b) -> u64 { return (b < 0 || a < b) ? 0ull : binom[a * kcols + b]; };
+        // (q <= 4: the 32-bit table serves, and neither the search nor the division in tp_split_cut is 64 bits wide)
+        auto C32 = [&](int a, int b) -> u64 { return b == 0 ? 1ull : (u64)tp_tri_c32[b - 1][a]; };
         const int total = tp_tri_cut_base[n_entries];
         for (int idx = tid; idx < total; idx += nt) {
             int lo = 0, hi = n_entries; // the entry whose range holds idx
@@ -1009,16 +1019,16 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
                 if ((int)tp_tri_cut_base[mid] <= idx) lo = mid;
                 else hi = mid;
             }
-            const int jt = plan->jt_hi - lo, np = (int)tp_tri_pieces[lo];
-            const int b_eff = tp_split_bstar(jt, b_star, q == 4);
-            tp_tri_cuts[idx] = (uint8_t)tp_split_cut(C, jt < b_eff ? jt : b_eff, q, np, idx - (int)tp_tri_cut_base[lo], true);
+            const int jt = jt_hi - lo, np = (int)tp_tri_pieces[lo], i = idx - (int)tp_tri_cut_base[lo];
+            const int b_eff = tp_split_bstar(jt, b_star, q == 4), jlow = jt < b_eff ? jt : b_eff;
+            tp_tri_cuts[idx] = (uint8_t)(q <= 4 ? tp_split_cut(C32, jlow, q, np, i, true) : tp_split_cut(C64, jlow, q, np, i, true));
         }
         if (q == 4)
             for (int idx = tid; idx < TP_TRI_MAX_HEADS * (TP_SPLIT_MAX_SUB + 1); idx += nt) {
                 const int b = idx / (TP_SPLIT_MAX_SUB + 1), sub = idx - b * (TP_SPLIT_MAX_SUB + 1);
-                if (b <= b_star || b >= plan->jt_hi || b + 2 > TP_MAX_N + 1) continue;
+                if (b <= b_star || b >= jt_hi || b + 2 > TP_MAX_N + 1) continue;
                 const int nsub = (int)tp_tri_cum[b + 2] - (int)tp_tri_cum[b];
-                if (nsub > 1 && sub <= nsub) tp_tri_lcuts[b][sub] = (uint8_t)tp_split_cut(C, b, q - 1, nsub, sub);
+                if (nsub > 1 && sub <= nsub) tp_tri_lcuts[b][sub] = (uint8_t)tp_split_cut(C32, b, q - 1, nsub, sub);
             }
     }
     TP_TRI_STAMP(4);
