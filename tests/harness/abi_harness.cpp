@@ -4,7 +4,8 @@
 // called from one goroutine per RPC (dpm/plugin.go:108-111, amdgpu.go:300-319).  No Go toolchain exists in this
 // image, so this C++ program issues the same sequence against the C ABI:
 //
-//     tp_create -> N sequential tp_allocate -> T threads x M concurrent tp_allocate -> tp_destroy
+//     tp_create -> N sequential tp_allocate -> T threads x M concurrent tp_allocate
+//               -> B threads x R concurrent tp_allocate_batch calls of 64 requests each -> tp_destroy
 //
 // and times every call with clock_gettime(CLOCK_MONOTONIC) around the ABI call itself (SURVEY 8(d) latency
 // protocol): no interpreter, no ctypes.  Beside it: the same request through the string-level policy class
@@ -12,7 +13,7 @@
 // (oracle/, linked here as the checker and CPU baseline -- test infrastructure, not product).
 // Every answer is compared with the oracle's.  Built by `make -C tests/harness` (also with -fsanitize=thread).
 //
-// usage: abi_harness <input file> [sequential calls] [threads] [calls per thread]      (input: see read_input)
+// usage: abi_harness <input file> [sequential calls] [threads] [calls per thread] [batch threads] [batches per thread]
 #include <algorithm>
 #include <atomic>
 #include <cstdio>
@@ -90,7 +91,7 @@ static bool read_input(const char *path, Input &in) {
 
 int main(int argc, char **argv) {
     if (argc < 2) {
-        fprintf(stderr, "usage: %s <input> [sequential calls] [threads] [calls per thread]\n", argv[0]);
+        fprintf(stderr, "usage: %s <input> [sequential calls] [threads] [calls per thread] [batch threads] [batches per thread]\n", argv[0]);
         return 2;
     }
     Input in;
@@ -99,7 +100,8 @@ int main(int argc, char **argv) {
         return 2;
     }
     const int n_seq = argc > 2 ? atoi(argv[2]) : 10000, n_thr = argc > 3 ? atoi(argv[3]) : 8,
-              n_per = argc > 4 ? atoi(argv[4]) : 2000;
+              n_per = argc > 4 ? atoi(argv[4]) : 2000, n_bthr = argc > 5 ? atoi(argv[5]) : 3,
+              n_bper = argc > 6 ? atoi(argv[6]) : 20;
 
     // ---- Init (tp_create through the policy class, as the Go Init would) -----------------------------
     tp::BestEffortPolicy pol;
@@ -191,11 +193,47 @@ int main(int argc, char **argv) {
     std::vector<double> conc;
     for (auto &v : per) conc.insert(conc.end(), v.begin(), v.end());
 
+    // ---- concurrent tp_allocate_batch calls on the same policy (two run at once, the others wait for a slot) ----
+    std::atomic<int> bad_batch{0};
+    std::vector<std::vector<double>> bper(n_bthr);
+    {
+        const int n_in_batch = 64;
+        std::vector<std::thread> ths;
+        for (int t = 0; t < n_bthr; t++)
+            ths.emplace_back([&, t] {
+                std::vector<tp_request> reqs(n_in_batch);
+                for (auto &r : reqs) {
+                    r.available = av.data();
+                    r.n_available = (int32_t)av.size();
+                    r.required = rq.data();
+                    r.n_required = (int32_t)rq.size();
+                    r.size = in.size;
+                }
+                const int stride = std::max(in.size, 1);
+                std::vector<int32_t> o((size_t)n_in_batch * stride), st(n_in_batch);
+                for (int i = 0; i < n_bper; i++) {
+                    const double t0 = now_us();
+                    const int rc = tp_allocate_batch(h, n_in_batch, reqs.data(), o.data(), stride, st.data(), nullptr);
+                    bper[t].push_back(now_us() - t0);
+                    if (rc != 0) bad_batch++;
+                    for (int r = 0; r < n_in_batch; r++) {
+                        if (st[r] != ref_n) bad_batch++;
+                        else
+                            for (int j = 0; j < ref_n; j++) bad_batch += in.devs[o[(size_t)r * stride + j]].Id != want[j];
+                    }
+                }
+            });
+        for (auto &th : ths) th.join();
+    }
+    std::vector<double> bat;
+    for (auto &v : bper) bat.insert(bat.end(), v.begin(), v.end());
+
     char tail[160];
     printf("{\"config\": \"%s\", \"devices\": %zu, \"available\": %zu, \"required\": %zu, \"size\": %d, \"subsets\": %llu, "
            "\"kernel\": %d, \"score\": %d, \"cpu_candidates\": %d, \"init_us\": %.0f, \"mismatches\": %d, ",
            in.name.c_str(), in.devs.size(), in.avail.size(), in.req.size(), in.size,
-           (unsigned long long)info.subsets_total, info.kernel, info.score, rres.n_candidates, init_us, bad + bad_conc.load());
+           (unsigned long long)info.subsets_total, info.kernel, info.score, rres.n_candidates, init_us,
+           bad + bad_conc.load() + bad_batch.load());
     print_stats("c_abi_sequential", stats(seq));
     printf(", ");
     print_stats("policy_strings_sequential", stats(strs));
@@ -203,8 +241,13 @@ int main(int argc, char **argv) {
     snprintf(tail, sizeof tail, ", \"threads\": %d, \"calls_per_s\": %.0f", n_thr, conc.size() / (conc_us * 1e-6));
     print_stats("c_abi_concurrent", stats(conc), tail);
     printf(", ");
+    if (!bat.empty()) {
+        snprintf(tail, sizeof tail, ", \"threads\": %d, \"requests_per_batch\": 64", n_bthr);
+        print_stats("c_abi_batch_concurrent", stats(bat), tail);
+        printf(", ");
+    }
     print_stats("cpu_reference_bfs", stats(cpu));
     printf(", \"clock\": \"clock_gettime(CLOCK_MONOTONIC) around each call, native caller\"}\n");
     ref_policy_free(ref);
-    return bad + bad_conc.load() ? 1 : 0;
+    return bad + bad_conc.load() + bad_batch.load() ? 1 : 0;
 }
