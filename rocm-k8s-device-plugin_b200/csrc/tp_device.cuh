@@ -4,6 +4,34 @@
 #pragma once
 #include "tp_kernels.cuh"
 
+// Opt `Kernel` in to the largest dynamic shared memory the current device allows (once per device) and check `need`
+// against it.  The attribute is per function, not per launch: setting it to what each launch needs lets two
+// host threads undo each other's value between the setting and the launch (two tp_allocate_batch calls, or two
+// tp_allocate calls with different requests, then fail with "invalid argument").  A value that never changes
+// cannot be undone.
+#include <atomic>
+template <auto Kernel>
+static cudaError_t tp_opt_in_max_smem(size_t need) {
+    static std::atomic<int> limit[64]; // per device ordinal; 0 = not asked yet
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    int lim = limit[dev].load(std::memory_order_acquire);
+    if (lim == 0) {
+        cudaFuncAttributes fa;
+        if ((e = cudaFuncGetAttributes(&fa, Kernel)) != cudaSuccess) return e;
+        int optin = 0;
+        if ((e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev)) != cudaSuccess) return e;
+        lim = optin - (int)fa.sharedSizeBytes;
+        if (lim <= 0) return cudaErrorInvalidValue;
+        if ((e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, lim)) != cudaSuccess) return e;
+        limit[dev].store(lim, std::memory_order_release); // (two threads may both get here: the same value)
+    }
+    return need <= (size_t)lim ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+
 typedef unsigned long long u64;
 
 // ---------------------------------------------------------------------------------------

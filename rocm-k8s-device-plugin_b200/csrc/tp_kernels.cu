@@ -395,7 +395,7 @@ cudaError_t tp_launch_family(const uint8_t *d_weight, int n_devices, const u64 *
     const int G = h.n_groups;
     const size_t smem = ((tp_smem_bytes(h.n, 1) + 15) & ~(size_t)15) + (size_t)G * G * 4 + (size_t)G * 4 +
                         (size_t)h.n * 4 + (size_t)h.n * G * 4;
-    cudaError_t e = cudaFuncSetAttribute(tp_family, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = tp_opt_in_max_smem<tp_family>(smem);
     if (e != cudaSuccess) return e;
     const u64 span = mask_hi - mask_lo;
     u64 blocks = (span + TP_FAMILY_THREADS - 1) / TP_FAMILY_THREADS;

@@ -927,8 +927,7 @@ static cudaError_t launch_split_md(const uint8_t *W, int nd, const u64 *binom, c
                                    unsigned *d_counter, int sm_count, cudaStream_t st, TpLaunchInfo *info,
                                    const TpBatch &batch) {
     const size_t smem = tp_split_smem_bytes(h.n, h.k, M, D);
-    cudaError_t e = cudaFuncSetAttribute(tp_exhaustive_split<M, D>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
+    cudaError_t e = tp_opt_in_max_smem<tp_exhaustive_split<M, D>>(smem);
     if (e != cudaSuccess) return e;
     e = cudaMemsetAsync(batch.count > 0 ? batch.grab : d_counter, 0, sizeof(unsigned), st);
     if (e != cudaSuccess) return e;

@@ -439,6 +439,93 @@ struct TpTriRows {
         }                                                                                               \
         [[fallthrough]];
 
+// ---- the quad stage: the values below TP_TRI_QB of the last walked position, without walking them ------------
+// Most prefixes are small (on 64 devices 42 % of the prefix pairs have their walked value below 9, with less
+// packed work than the ~330 instructions a pair costs before its first row), so for the values b0 < TP_TRI_QB the
+// walked position joins the table: S4 = S3[b][jx][jy] + W[b0][b] + W[b0][jx] + W[b0][jy], low half for b0, high
+// half for b0 - 1 (TP_BIG where b = b0 - 1, and for the head 3, which has no partner), one table per pair with an
+// odd head b0 = 3, 5, .. < TP_TRI_QB, leaves 2 .. b0 - 1 in the row layout of the S3 leaves.  The lane registers
+// then hold VU = V + T_L SPLATTED (they do not depend on b0 any more: built once for the whole range), and
+//     score = base + VU[b0] + VU[b] + VU[jx] + VU[jy] + S4 .
+// A pair that reports is walked again by the ordinary code (T', T'', the leaf loop), which finds the candidate.
+#ifndef TP_TRI_QB
+#define TP_TRI_QB 8 /* even; 0 switches the stage off.  Measured 0 / 8 / 10 / 12 / 16: 8 of 80 1.445 / 1.414 / 1.447 /
+                      1.437 / 1.503 ms, block-per-request 8-of-48 searches 1.24 / 1.31 / 1.31 / 1.33 / 1.32e13 subsets/s,
+                      8 of 64 unchanged (0.282 ms): the stage's code competes for the same instruction cache */
+#endif
+__host__ __device__ constexpr int tp_tri_q_leaf_words(int b) { return (tp_tri_c2(b) + 3) & ~3; }
+// word offset of leaf b in the table of the pair with the odd head b0
+__host__ __device__ constexpr int tp_tri_q_off(int b0, int b) {
+    int s = 0;
+    for (int h = 3; h < b0; h += 2)
+        for (int l = 2; l < h; l++) s += tp_tri_q_leaf_words(l);
+    for (int l = 2; l < b; l++) s += tp_tri_q_leaf_words(l);
+    return s;
+}
+#define TP_TRI_Q_WORDS (TP_TRI_QB >= 4 ? tp_tri_q_off(TP_TRI_QB + 1, 2) : 4)
+static __shared__ __align__(16) uint32_t tp_tri_q4[TP_TRI_Q_WORDS];
+
+// One pair (B0, B0 - 1): the best total below the walked position per half, the pair's own terms added.
+template <int B0>
+__device__ __forceinline__ unsigned tp_tri_qpair(const unsigned (&Q)[TP_TRI_NREG], unsigned qt) {
+    unsigned xp = 0xFFFFFFFFu;
+    tp_static_for<2, B0>([&](auto ib) {
+        constexpr int B = decltype(ib)::value;
+        unsigned runA = TP_BIG2 + TP_BIG2, runB = TP_BIG2 + TP_BIG2;
+        TpTriRows<B - 1>::run(Q, qt + (unsigned)tp_tri_q_off(B0, B) * 4u, runA, runB);
+        xp = __vimin3_u16x2(xp, runA + Q[B], runB + Q[B]);
+    });
+    return xp + __byte_perm(Q[B0], Q[B0 - 1], 0x5410);
+}
+#define TP_TRI_QCASE(B0)                                                        \
+    case B0:                                                                    \
+        if constexpr ((B0) < TP_TRI_QB) {                                       \
+            if (__vminu2(tp_tri_qpair<(B0)>(Q, qt), room2) != room2) bits |= 1u << ((B0) >> 1); \
+        }                                                                       \
+        [[fallthrough]];
+// The pairs with heads q_top, q_top - 2, .., 3; bit (head >> 1) of the result: this lane has a candidate in that pair.
+// va, tl: this lane's V and the level's T vector; room2: the threshold in both halves.
+__device__ __forceinline__ unsigned tp_tri_quads(unsigned va, unsigned tl, unsigned room2, int q_top) {
+    unsigned Q[TP_TRI_NREG]; // positions 0 .. TP_TRI_QB - 1 are used
+    {
+        const uint4 v0 = tp_lds128v(va), v1 = tp_lds128v(va + 512), t0 = tp_lds128v(tl), t1 = tp_lds128v(tl + 16);
+        const unsigned x[8] = {v0.x + t0.x, v0.y + t0.y, v0.z + t0.z, v0.w + t0.w,
+                               v1.x + t1.x, v1.y + t1.y, v1.z + t1.z, v1.w + t1.w};
+#pragma unroll
+        for (int m = 0; m < 8; m++) {
+            Q[2 * m] = __byte_perm(x[m], 0, 0x1010);
+            Q[2 * m + 1] = __byte_perm(x[m], 0, 0x3232);
+        }
+    }
+    const unsigned qt = (unsigned)__cvta_generic_to_shared(tp_tri_q4);
+    unsigned bits = 0;
+    switch (q_top) {
+        TP_TRI_QCASE(15) TP_TRI_QCASE(13) TP_TRI_QCASE(11) TP_TRI_QCASE(9) TP_TRI_QCASE(7) TP_TRI_QCASE(5) TP_TRI_QCASE(3)
+    default: break;
+    }
+    return bits;
+}
+
+// The S4 tables of the quad stage from the plain table wp (reversed positions): a thread per (pair, leaf).
+static __device__ void tp_tri_build_quads(const uint16_t *wp, int rsp, int n_pos) {
+    for (int c = threadIdx.x; c < (TP_TRI_QB / 2) * TP_TRI_QB; c += blockDim.x) {
+        const int h = 3 + 2 * (c / TP_TRI_QB), b = c % TP_TRI_QB; // head of the pair, leaf
+        if (h >= TP_TRI_QB || b < 2 || b >= h) continue;
+        uint32_t *dst = tp_tri_q4 + tp_tri_q_off(h, b);
+        const bool hi_ok = h - 1 >= 3 && b < h - 1 && h < n_pos; // the second prefix of the pair exists and has this leaf
+        const uint16_t *r0 = wp + h * rsp, *r1 = wp + (h - 1) * rsp, *rb = wp + b * rsp;
+        int w = 0;
+        for (int jx = 1; jx < b; jx++)
+            for (int jy = 0; jy < jx; jy++, w++) {
+                const unsigned s3 = (unsigned)rb[jx] + rb[jy] + wp[jx * rsp + jy];
+                const unsigned lo = h < n_pos ? s3 + r0[b] + r0[jx] + r0[jy] : TP_BIG;
+                const unsigned hi = hi_ok ? s3 + r1[b] + r1[jx] + r1[jy] : TP_BIG;
+                dst[w] = lo | (hi << 16);
+            }
+        for (; w < tp_tri_q_leaf_words(b); w++) dst[w] = TP_BIG2;
+    }
+}
+
 // All leaves b in [lo_leaf, hi_leaf) of a pair of walked prefixes, hi the walked value of the first one (leaves are
 // below it; the second prefix is without leaf hi - 1); the range is all of [2, hi) except in an item that holds one
 // walked value cut by its leaves.  va, t1, tbl:
@@ -541,7 +628,28 @@ struct TpTriWalk {
             // an item that holds a single first walked value may be cut by the position below it: here, the leaves
             const int lo_leaf = L == 0 ? max(2, (int)tp_lds8v(bst + 8)) : 2;
             const int cap_leaf = L == 0 ? (int)tp_lds8v(bst + 9) : TP_MAX_N;
-            for (int b = hi - 1; b >= lo; b -= 2) {
+            // The values below TP_TRI_QB go through the quad stage first (a range that starts at 3 only: the lowest
+            // slice of a pivot); the pairs it reports are walked again below, after the rest of the range.
+            unsigned qmask = 0;
+            int lo_cur = lo;
+            if (TP_TRI_QB >= 4 && lo <= 3 && hi >= 4) {
+                const int top = min(hi, TP_TRI_QB) - 1, q_top = (top & 1) ? top : top - 1; // the largest odd head
+                const int room = *(volatile int *)&tp_tri_bound - (lb + sb) + 1;
+                const unsigned room2 = w.gcap_active > 0 ? (unsigned)min(max(room, 0), (int)TP_BIG - 1) * 0x10001u : 0u;
+                qmask = __reduce_or_sync(0xFFFFFFFFu, tp_tri_quads(va, tl, room2, q_top));
+                lo_cur = q_top + 1;
+            }
+            bool again = false; // walking the reported pairs of the quad stage
+            for (int b = hi - 1;; b -= 2) {
+                if (!again && b < lo_cur) again = true;
+                if (again) {
+                    if (!qmask) break;
+                    const int t = 31 - __clz((int)qmask);
+                    qmask ^= 1u << t;
+                    b = 2 * t + 1;
+                    lo_cur = t == 1 ? 3 : b - 1; // (the head 3 has no partner)
+                }
+                const int lo = lo_cur;
                 const int b1 = b - 1; // (a position even when it is below lo: lo >= 3)
                 const int base0 = lb + v_at(b) + sb + (int)tp_lds16v(tl + 2u * b);
                 const int base1 = b1 >= lo ? lb + v_at(b1) + sb + (int)tp_lds16v(tl + 2u * b1) : -1;
@@ -1032,6 +1140,7 @@ __device__ __noinline__ void tp_tri_setup(const uint8_t *__restrict__ W, int nd,
             }
     }
     TP_TRI_STAMP(4);
+    if (TP_TRI_QB >= 4) tp_tri_build_quads(wp, rsp, n);
     tp_tri_build_table(tbl, gcap, wp, rsp);
     TP_TRI_STAMP(5);
     for (int i = lane; i < M; i += 32) tstack[i] = t0[i];
@@ -1138,8 +1247,7 @@ static cudaError_t launch_tri_md(const uint8_t *W, int nd, const u64 *binom, con
                                  unsigned *d_counter, int sm_count, cudaStream_t st, TpLaunchInfo *info,
                                  const TpBatch &batch) {
     const size_t smem = tp_tri_smem_bytes_md<M, DW>(h.n, h.k, gcap);
-    cudaError_t e = cudaFuncSetAttribute(tp_exhaustive_tri<M, DW>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
+    cudaError_t e = tp_opt_in_max_smem<tp_exhaustive_tri<M, DW>>(smem);
     if (e != cudaSuccess) return e;
     if (batch.count > 0) { // (a single request's counter words are re-armed by the kernel itself)
         e = cudaMemsetAsync(batch.grab, 0, sizeof(unsigned), st);

@@ -111,6 +111,40 @@ def test_concurrent_callers():
     pol.close()
 
 
+def test_concurrent_callers_with_different_shared_memory_needs():
+    """Threads whose requests need the same kernels with different dynamic shared memory (8 of 20 .. 8 of 60 through
+    TRI, 5 of n through SPLIT): the opt-in of a kernel's shared memory must not depend on who launched last."""
+    ref, pol, ids = make("cpx")
+    gen = topo.SplitMix64(0xD1FF)
+    reqs = []
+    for i in range(96):
+        n = 20 + gen.below(41)
+        av = sorted(ids, key=lambda _: gen.below(1 << 30))[:n]
+        av = [x for x in ids if x in set(av)]
+        reqs.append((av, [], 8 if i % 3 else 5))
+    want = [ref.Allocate(*r) for r in reqs]
+    got = [None] * len(reqs)
+    errors = []
+
+    def worker(t):
+        try:
+            for i in range(t, len(reqs), 6):
+                av, rq, k = reqs[i]
+                out, _ = tp.allocate_indices(pol, pol.indices(av), pol.indices(rq), k)
+                got[i] = [pol.devices[j].Id for j in out]
+        except Exception as e:  # noqa: BLE001 -- reported below
+            errors.append(repr(e))
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(6)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+    assert got == want
+    pol.close()
+
+
 def test_build_weights_on_gpu():
     devs, pairs = topo.hives_topology()
     n = len(devs)
