@@ -168,9 +168,9 @@ __device__ __forceinline__ void tp_tri_rowpair_pf(const unsigned (&VT)[TP_TRI_NR
     if constexpr (H > 0) runB = __viaddmin_u16x2(accB, VT[JB], runB);
 }
 
-#define TP_TRI_CASE(H)                                              \
-    case H:                                                         \
-        tp_tri_rowpair_pf<(H)>(VT, tl, runA, runB, bufA, bufB);     \
+#define TP_TRI_CASE(H)                                                                         \
+    case H:                                                                                    \
+        if constexpr ((H) < TP_TRI_GC) tp_tri_rowpair_pf<(H)>(VT, tl, runA, runB, bufA, bufB); \
         [[fallthrough]];
 #define TP_TRI_CASE8(B)                                                                          \
     TP_TRI_CASE(B + 7) TP_TRI_CASE(B + 6) TP_TRI_CASE(B + 5) TP_TRI_CASE(B + 4) TP_TRI_CASE(B + 3) \
@@ -193,9 +193,9 @@ __device__ __forceinline__ void tp_tri_vt_chunk(unsigned (&VT)[TP_TRI_NREG], uns
     VT[8 * C + 6] = __byte_perm(x3, y3, 0x5410);
     VT[8 * C + 7] = __byte_perm(x3, y3, 0x7632);
 }
-#define TP_TRI_VT_CASE(C)                           \
-    case (C) + 1:                                   \
-        tp_tri_vt_chunk<(C)>(VT, va, t1, 2u * M);   \
+#define TP_TRI_VT_CASE(C)                                                            \
+    case (C) + 1:                                                                    \
+        if constexpr (8 * (C) < TP_TRI_NREG) tp_tri_vt_chunk<(C)>(VT, va, t1, 2u * M); \
         [[fallthrough]];
 
 // What the hot loop does not need in registers lives here: the block's tables (written once per

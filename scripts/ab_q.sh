@@ -11,4 +11,5 @@ for tag in "$@"; do
   done
   timeout 100 python scripts/tri_sweep.py 48 56 2>&1 | grep "kernel tri"
   timeout 200 python scripts/batch_probe.py | grep -E "8 of (48|56)" | cut -c1-140
+  timeout 200 python scripts/shard_sweep2.py 2>/dev/null | head -3
 done
