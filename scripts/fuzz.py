@@ -1,6 +1,6 @@
 """Differential fuzz on the GPU: random topologies (group sizes, NUMA, link types, missing links)
 and random requests; every answer must equal the oracle's BFS.  usage: fuzz.py <seconds> [seed]"""
-import os, sys, time
+import math, os, sys, time
 R = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, R); sys.path.insert(0, os.path.join(R, "tests"))
 import topo
@@ -10,7 +10,7 @@ tp = package()
 budget = float(sys.argv[1]) if len(sys.argv) > 1 else 60
 gen = topo.SplitMix64(int(sys.argv[2], 0) if len(sys.argv) > 2 else 0xF022)
 t_end = time.time() + budget
-n_topo = n_req = 0
+n_topo = n_req = n_batch = 0
 kernels = {}
 while time.time() < t_end:
     groups = 2 + gen.below(11)
@@ -48,7 +48,6 @@ while time.time() < t_end:
     for _ in range(40):
         av, rq, k = topo.random_request(gen, ids, kmax=min(9, len(ids) - 1), p_choices=(0.3, 0.6, 0.9), max_required=3)
         # keep the oracle's BFS (k-permutations on unpartitioned nodes) and the GPU search bounded
-        import math
         if math.comb(len(av), k) > 3e9 or (groups > 8 and k > 6):
             continue
         want = ref.Allocate(av, rq, k)
@@ -63,7 +62,23 @@ while time.time() < t_end:
             if spl.Allocate(av, rq, k) != want or spl.last["key"] != pol.last["key"]:
                 print("SPLIT/TRI MISMATCH", dict(av=av, rq=rq, k=k, split=spl.last, default=pol.last))
                 sys.exit(1)
+    if n_topo % 5 == 0:  # the same kind of requests through ONE tp_allocate_batch call (block-per-request kernels, shares)
+        reqs = []
+        while len(reqs) < 24:
+            av, rq, k = topo.random_request(gen, ids, kmax=min(9, len(ids) - 1), p_choices=(0.3, 0.6, 0.9), max_required=3)
+            if math.comb(len(av), k) > 3e8 or (groups > 8 and k > 6):
+                continue
+            reqs.append((av, rq, k))
+        if n_topo % 10 == 0:
+            pol.set_batch_tuning(share_shift=20 + gen.below(6), items_per_warp=1 + gen.below(8))
+        got, _ = tp.allocate_batch(pol, reqs)
+        for r, g in zip(reqs, got):
+            want = ref.Allocate(*r)
+            if g != want:
+                print("BATCH MISMATCH", dict(groups=groups, n=len(devs), req=r, got=g, want=want))
+                sys.exit(1)
+        n_batch += len(reqs)
     pol.close()
     if spl is not None:
         spl.close()
-print(f"fuzz ok: {n_topo} topologies, {n_req} requests, kernels {kernels}")
+print(f"fuzz ok: {n_topo} topologies, {n_req} requests, kernels {kernels}, {n_batch} requests in batches")
