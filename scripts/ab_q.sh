@@ -9,7 +9,5 @@ for tag in "$@"; do
     timeout 100 python scripts/run_one.py cpx64 8 10 | cut -c1-70
     timeout 100 python scripts/run_one.py c4 8 10 | cut -c1-70
   done
-  timeout 100 python scripts/tri_sweep.py 48 56 2>&1 | grep "kernel tri"
   timeout 200 python scripts/batch_probe.py | grep -E "8 of (48|56)" | cut -c1-140
-  timeout 200 python scripts/shard_sweep2.py 2>/dev/null | head -3
 done
